@@ -1,0 +1,147 @@
+/*
+ * psascan_cuda.h -- C ABI of libpsascan_cuda.so, the B200 (sm_100a) implementation of the
+ * pSAscan hot path.  One export per seam of the reference (pdinklag/psascan); citations are
+ * file:line into the reference tree.  Plain pointers and sizes only.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative PSC_E* code on error; the message of
+ *     the last error on the calling thread is psc_last_error().  (The reference prints and
+ *     exits, e.g. src/utils.cpp:60-63; the host wrapper host/psascan.hpp does that.)
+ *   - pointers are HOST pointers unless the name ends in _d (device pointers on the GPU the
+ *     context was created on).
+ *   - gt bit vectors cross this boundary in the reference's layout: reversed, LSB-first
+ *     (include/bitvector.hpp:61-67): for a vector covering text positions (lo, hi], bit r
+ *     of byte r>>3 (mask 1 << (r & 7)) belongs to position hi - r, r in [0, hi-lo).
+ *   - block-relative suffix array entries are uint32 (blocks are < 2^32 - 2^12 symbols).
+ *   - there is no CPU fallback: without a usable CUDA device every call fails with
+ *     PSC_ECUDA.
+ */
+#ifndef PSASCAN_CUDA_H
+#define PSASCAN_CUDA_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PSC_OK 0
+#define PSC_EARG (-1)      /* bad argument */
+#define PSC_ECUDA (-2)     /* CUDA runtime error / no device */
+#define PSC_ESENTINEL (-3) /* byte 255 in the text (initial_partial_sufsort.hpp:70-75) */
+#define PSC_ENOMEM (-4)    /* HBM budget exceeded */
+
+typedef struct psc_context psc_context; /* one GPU, its streams and scratch memory */
+typedef struct psc_rank psc_rank;       /* device rank structure over one block BWT */
+
+const char *psc_last_error(void);
+int psc_version(void);
+
+/* Device / stream setup; nothing in the reference corresponds (psascan.hpp:53-131 only
+ * budgets host RAM).  device < 0: current device.  hbm_budget = 0: all free memory. */
+int psc_init(int device, size_t hbm_budget, psc_context **ctx);
+int psc_shutdown(psc_context *ctx);
+/* Largest block length (symbols) the budget allows for a text of n symbols whose SA is
+ * assembled on the device: replaces max_block_size = ram/5.2 (psascan.hpp:91). */
+long psc_max_block_size(psc_context *ctx, long n);
+
+/* ---- stage 1: inmem_psascan<saidx_t,12>()  inmem_psascan_src/inmem_psascan.hpp:64-80,
+ * called at partial_sufsort.hpp:166-168, 286-288.
+ * Sorts the suffixes of text[0..m) as suffixes of the whole text.
+ *   tail_prefix[tail_prefix_len]  the text right after the block (min(m, tail) symbols
+ *                                 suffice, inmem_psascan.hpp:150-156); NULL/0 for the last block
+ *   tail_gt_rev   gt bits of positions (end, end + tail_prefix_len] relative to `end`
+ *                 (suffix(j) > suffix(end)), reversed layout with hi = end+tail_prefix_len;
+ *                 NULL when tail_prefix_len == 0
+ *   text_after    1 if any text follows the block (tail_prefix_len > 0 is implied)
+ *   sa_out[m]     block-relative SA                       (required)
+ *   bwt_out[m]    BWT with 0 at i0 (inmem_bwt_from_sa.hpp:48-56); may be NULL
+ *   gt_begin_rev  m bits, positions (0, m] relative to the block start, reversed layout with
+ *                 hi = m (change_gt_reference_point.hpp:62-118); may be NULL
+ *   i0            rank of the block's first suffix */
+int psc_sort_block(psc_context *ctx, const uint8_t *text, long m,
+                   const uint8_t *tail_prefix, long tail_prefix_len,
+                   const uint8_t *tail_gt_rev,
+                   uint32_t *sa_out, uint8_t *bwt_out, uint8_t *gt_begin_rev, long *i0);
+
+/* ---- stage 3a: rank4n ctor / dtor / m_count   rank.hpp:115-136, 710, 112.
+ * i0 < 0: bwt holds no placeholder.  counts[c] = occurrences of c in bwt, the placeholder
+ * NOT counted (the reference counts it as a 0 and compute_gap.hpp:80 takes it out again). */
+int psc_rank_build(psc_context *ctx, const uint8_t *bwt, long m, long i0, psc_rank **rank);
+int psc_rank_counts(const psc_rank *rank, long counts[256]);
+/* rank(i, c)  rank.hpp:566-708, batched: out[k] = #c[k] in bwt[0..i[k]) (placeholder excluded) */
+int psc_rank_query(psc_context *ctx, const psc_rank *rank, long nq, const long *i,
+                   const uint8_t *c, long *out);
+int psc_rank_free(psc_context *ctx, psc_rank *rank);
+
+/* ---- stage 2: em_compute_initial_ranks()  em_compute_initial_ranks.hpp:222-319, 513-561.
+ * out[k] = number of suffixes of the block smaller than suffix(starts[k]).
+ *   block_text[m], block_sa[m]      the block and its SA
+ *   after_text[after_len]           the text from the block end on (pattern source)
+ *   starts[k]                       pattern k begins at after_text[starts[k]], 0 <= starts[k] <= after_len
+ *   text_end_after                  1 if after_text reaches the end of the whole text
+ *   after_gt_rev                    gt bits of positions (0, after_len] of after_text relative
+ *                                   to its position 0 (= block end), reversed layout hi = after_len */
+int psc_initial_ranks(psc_context *ctx, const uint8_t *block_text, const uint32_t *block_sa,
+                      long m, const uint8_t *after_text, long after_len,
+                      const uint8_t *after_gt_rev, long nstarts, const long *starts, long *out);
+
+/* ---- stage 3b: compute_gap()  compute_gap.hpp:61-157 + stream.hpp:147-158 + update.hpp:86-96.
+ * Streams tail[0..t) right to left against the block's rank structure.
+ *   i0, last      rank of the block's first suffix; last symbol of the block
+ *   block_counts  counts[c] of the block TEXT symbols (= rank counts + last), C array is
+ *                 derived inside (compute_gap.hpp:77-85)
+ *   nwalk, walk_beg[nwalk+1]  walker k streams tail[walk_beg[k]..walk_beg[k+1]) starting from
+ *                 start_rank[k] = rank of suffix(tail + walk_beg[k+1]); interior boundaries
+ *                 must be multiples of 32
+ *   gt_in_rev     gt bits of tail positions (0, t] relative to the block END, reversed, hi = t
+ *   gt_out_rev    out: gt bits of tail positions (0, t] relative to the block BEGIN; may be NULL
+ *   gap[m+1]      out: gap[i] = number of tail suffixes with rank i (uint32 counters, ADDED to) */
+int psc_compute_gap(psc_context *ctx, const psc_rank *rank, long i0, uint8_t last,
+                    const long block_counts[256], const uint8_t *tail, long t,
+                    long nwalk, const long *walk_beg, const long *start_rank,
+                    const uint8_t *gt_in_rev, uint8_t *gt_out_rev, uint32_t *gap);
+
+/* ---- stage 4: merge()  merge.hpp:54-180 (one level of it; the host cascades right to left).
+ * Interleaves a block SA with the already merged suffixes of everything right of it:
+ *   out[u + S(u)] = beg + sa[u],  S = inclusive scan of gap;  the right_len entries of
+ *   `right` fill the remaining slots in order.  out has m + right_len entries of 5 bytes
+ *   (types/uint40.hpp:42-46).  right is 5-byte entries too. */
+int psc_merge_level(psc_context *ctx, const uint32_t *sa, const uint32_t *gap, long m, long beg,
+                    const uint8_t *right_sa5, long right_len, uint8_t *out_sa5);
+
+/* ---- glue for a block sorted as two pieces: gap_array.hpp:273-364 (gap -> bitvector),
+ * bwt_merge.hpp:66-140, compute_left_gap.hpp:162-306, compute_right_gap.hpp:161-305.
+ * bv has len_l + len_r bits, LSB-first, FORWARD (bitvector.hpp:61-67 without reversal). */
+int psc_gap_to_bitvector(psc_context *ctx, const uint32_t *gap_l, long len_l, long len_r,
+                         uint8_t *bv);
+int psc_merge_bwt(psc_context *ctx, const uint8_t *bwt_l, const uint8_t *bwt_r, long len_l,
+                  long len_r, long i0_l, long i0_r, uint8_t last_l, const uint8_t *bv,
+                  uint8_t *bwt_out, long *i0_out);
+int psc_split_gap(psc_context *ctx, const uint8_t *bv, long len_l, long len_r,
+                  const uint32_t *block_gap, uint64_t *left_gap, uint64_t *right_gap);
+
+/* ---- the whole path: partial_sufsort() + merge()  partial_sufsort.hpp:559-584,
+ * merge.hpp:54-55 as called from psascan.hpp:117-125.  text[n] -> out_sa5[5n].
+ * max_block = 0: psc_max_block_size().  Text stays resident in HBM between stages. */
+int psc_construct_sa(psc_context *ctx, const uint8_t *text, long n, long max_block,
+                     uint8_t *out_sa5);
+/* same with device buffers (text_d[n], out_sa5_d[5n]); used for the HBM-resident timing */
+int psc_construct_sa_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
+                       uint8_t *out_sa5_d);
+
+/* per-phase device time (ms, CUDA events) and counters of the last psc_construct_sa* call */
+typedef struct psc_stats {
+  double ms_total, ms_gt_end, ms_sort, ms_radix, ms_bwt, ms_rank_build, ms_init_ranks, ms_walk,
+      ms_merge, ms_h2d, ms_d2h;
+  long n_blocks, lf_steps, radix_passes, radix_elems, doubling_rounds, walkers, kernel_launches;
+} psc_stats;
+int psc_get_stats(psc_context *ctx, psc_stats *out);
+
+/* micro-benchmarks used for the roofline denominators (SURVEY.md 8-d "R32") */
+int psc_bench_random_sectors(psc_context *ctx, size_t bytes, int iters, double *gbs);
+int psc_bench_radix_pass(psc_context *ctx, long n, int iters, double *ms_per_pass);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,252 @@
+// api.cu -- the C ABI (include/psascan_cuda.h) and the block pipeline that keeps everything in HBM.
+#include <stdarg.h>
+#include <algorithm>
+#include "common.cuh"
+
+namespace psc {
+
+static thread_local char g_err[1024] = "";
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+template <typename F>
+static int guarded(F &&f) {
+  try {
+    f();
+    return PSC_OK;
+  } catch (const CudaError &e) {
+    return e.code;
+  } catch (const std::exception &e) {
+    set_error("%s", e.what());
+    return PSC_ECUDA;
+  }
+}
+
+static void arg_check(bool ok, const char *what) {
+  if (!ok) { set_error("bad argument: %s", what); throw CudaError{PSC_EARG}; }
+}
+
+__global__ void or_not_bit_kernel(const uint32_t *src_bits, long src_idx, int src_default,
+                                  uint32_t *dst_bits, long dst_idx) {
+  // dst[dst_idx] |= !src[src_idx]   (src == null: src bit = src_default)
+  bool s = src_bits ? bit_get(src_bits, src_idx) : (src_default != 0);
+  if (!s) atomicOr(&dst_bits[dst_idx >> 5], 1u << (dst_idx & 31));
+}
+
+// walker layout for a tail of t symbols: equal slices, boundaries on multiples of 32
+static void plan_walkers(psc_context *ctx, long t, std::vector<uint64_t> *beg) {
+  long target = (long)ctx->n_sm * 2048;
+  if (const char *e = getenv("PSC_WALKERS")) target = std::max(1L, atol(e));
+  long slice = div_up(t, target);
+  slice = std::max(64L, div_up(slice, 32) * 32);
+  long W = div_up(t, slice);
+  beg->resize(W + 1);
+  for (long k = 0; k < W; ++k) (*beg)[k] = (uint64_t)(k * slice);
+  (*beg)[W] = (uint64_t)t;
+}
+
+// Stages 2+3 for one block against the text after it (all device pointers).
+//   gt_cur: bits relative to the block end, bit index = global position - 1 - bit_base
+static void gap_of_block(psc_context *ctx, const uint8_t *block_d, long m, const uint32_t *sa_d,
+                         long i0, const uint8_t *after_d, long t, const uint32_t *gt_cur, long gt_off,
+                         uint32_t *gt_new, uint32_t *gap_d) {
+  uint8_t last;
+  PSC_CUDA(cudaMemcpyAsync(&last, block_d + m - 1, 1, cudaMemcpyDeviceToHost, ctx->stream));
+  DevBuf<uint8_t> bwt(ctx, m);
+  bwt_from_sa(ctx, block_d, sa_d, m, bwt.p);
+  psc_rank *rk = rank_build(ctx, bwt.p, m, i0);
+  bwt.release();
+  try {
+    uint64_t Cmap[256], run = 0;
+    for (int c = 0; c < 256; ++c) { Cmap[c] = run; run += (uint64_t)rk->counts[c] + (c == last ? 1 : 0); }
+    std::vector<uint64_t> wb;
+    plan_walkers(ctx, t, &wb);
+    long W = (long)wb.size() - 1;
+    DevBuf<uint64_t> wb_d(ctx, W + 1), sr_d(ctx, W);
+    h2d(ctx, wb_d.p, wb.data(), wb.size());
+    // walker k starts from the rank of suffix(after + wb[k+1]); the last one from suffix(n): 0
+    initial_ranks(ctx, block_d, sa_d, m, after_d, t, 1, gt_cur, gt_off, W, wb_d.p + 1, sr_d.p);
+    lf_walk(ctx, rk, (uint32_t)i0, last, Cmap, after_d, t, W, wb_d.p, sr_d.p, gt_cur, gt_off, gt_new,
+            gt_off, gap_d);
+    sync(ctx);
+  } catch (...) {
+    rank_free(rk);
+    throw;
+  }
+  rank_free(rk);
+}
+
+static void construct_sa_device(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
+                                uint8_t *out_sa5_d) {
+  memset(&ctx->stats, 0, sizeof(ctx->stats));
+  ctx->launches = 0;
+  if (n == 0) return;
+  PhaseTimer total(ctx, &ctx->stats.ms_total);
+  if (max_block <= 0) max_block = psc_max_block_size(ctx, n);
+  arg_check(max_block > 0, "text does not fit the HBM budget");
+  max_block = std::min(max_block, (1L << 31) - 4096);
+  long B = div_up(n, max_block);
+  ctx->stats.n_blocks = B;
+  long gwords = (n + 1 + 31) / 32 + 2;
+  DevBuf<uint32_t> Ga, Gb;
+  DevBuf<uint32_t> Mlo[2];
+  DevBuf<uint8_t> Mhi[2];
+  if (B > 1) {
+    Ga.alloc(ctx, gwords); Gb.alloc(ctx, gwords);
+    Ga.zero(); Gb.zero();
+    for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); Mhi[k].alloc(ctx, n); }
+  } else {
+    Mlo[0].alloc(ctx, n); Mhi[0].alloc(ctx, n);
+  }
+  uint32_t *gt_cur = Ga.p, *gt_new = Gb.p;
+  int cur = 0;
+  long right_len = 0;
+  for (long id = B - 1; id >= 0; --id) {
+    long beg = id * max_block, end = std::min(n, beg + max_block), m = end - beg, t = n - end;
+    const uint8_t *block_d = text_d + beg, *after_d = text_d + end;
+    BlockSortResult res;
+    {
+      DevBuf<uint32_t> gt_end;
+      if (t > 0) {
+        gt_end.alloc(ctx, m / 32 + 2);
+        compute_gt_end(ctx, block_d, m, after_d, t, 1, gt_cur, end, gt_end.p);
+      }
+      sort_block(ctx, block_d, m, t > 0 ? gt_end.p : nullptr, &res);
+      if (id > 0) {
+        PSC_CUDA(cudaMemsetAsync(gt_new, 0, gwords * 4, ctx->stream));
+        gt_begin_from_isa(ctx, res.isa.p, m, (uint32_t)res.i0, gt_new, beg);
+        or_not_bit_kernel<<<1, 1, 0, ctx->stream>>>(t > 0 ? gt_end.p : nullptr, 0, 1, gt_new, end - 1);
+        PSC_LAUNCH_CHECK();
+        ctx->launches++;
+      }
+    }
+    res.isa.release();
+    DevBuf<uint32_t> gap;
+    if (t > 0) {
+      gap.alloc(ctx, m + 1);
+      gap.zero();
+      gap_of_block(ctx, block_d, m, res.sa.p, res.i0, after_d, t, gt_cur, end, id > 0 ? gt_new : nullptr,
+                   gap.p);
+    }
+    int nxt = B > 1 ? 1 - cur : 0;
+    merge_level(ctx, res.sa.p, gap.p, m, beg, Mlo[cur].p, Mhi[cur].p, right_len, Mlo[nxt].p, Mhi[nxt].p);
+    cur = nxt;
+    right_len += m;
+    std::swap(gt_cur, gt_new);
+  }
+  pack_sa5(ctx, Mlo[cur].p, Mhi[cur].p, n, out_sa5_d);
+  sync(ctx);
+  ctx->stats.kernel_launches = ctx->launches;
+}
+
+}  // namespace psc
+
+using namespace psc;
+
+extern "C" {
+
+const char *psc_last_error(void) { return g_err; }
+int psc_version(void) { return 100; }
+
+int psc_init(int device, size_t hbm_budget, psc_context **out) {
+  if (!out) { set_error("psc_init: null out pointer"); return PSC_EARG; }
+  *out = nullptr;
+  return guarded([&] {
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+      cudaGetLastError();
+      set_error("no CUDA device: %s (this library has no CPU fallback)",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+      throw CudaError{PSC_ECUDA};
+    }
+    if (device < 0) PSC_CUDA(cudaGetDevice(&device));
+    PSC_CUDA(cudaSetDevice(device));
+    psc_context *c = new psc_context();
+    c->device = device;
+    cudaDeviceProp prop;
+    PSC_CUDA(cudaGetDeviceProperties(&prop, device));
+    c->n_sm = prop.multiProcessorCount;
+    PSC_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    PSC_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+    PSC_CUDA(cudaDeviceGetDefaultMemPool(&c->pool, device));
+    uint64_t thr = UINT64_MAX;
+    PSC_CUDA(cudaMemPoolSetAttribute(c->pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    c->hbm_budget = hbm_budget;
+    memset(&c->stats, 0, sizeof(c->stats));
+    *out = c;
+  });
+}
+
+int psc_shutdown(psc_context *ctx) {
+  if (!ctx) return PSC_OK;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  cudaMemPoolTrimTo(ctx->pool, 0);
+  cudaStreamDestroy(ctx->stream);
+  cudaStreamDestroy(ctx->side);
+  delete ctx;
+  return PSC_OK;
+}
+
+long psc_max_block_size(psc_context *ctx, long n) {
+  if (!ctx || n <= 0) return 0;
+  size_t free_b = 0, total_b = 0;
+  cudaSetDevice(ctx->device);
+  if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 0;
+  uint64_t reserved = 0;
+  cudaMemPoolGetAttribute(ctx->pool, cudaMemPoolAttrReservedMemCurrent, &reserved);
+  uint64_t used = 0;
+  cudaMemPoolGetAttribute(ctx->pool, cudaMemPoolAttrUsedMemCurrent, &used);
+  double avail = (double)free_b + (double)(reserved - used);
+  if (ctx->hbm_budget && (double)ctx->hbm_budget < avail) avail = (double)ctx->hbm_budget;
+  avail *= 0.92;
+  // single block: text + output + 40 B/symbol of sort state
+  if ((double)n * 52.0 <= avail && n <= (1L << 31) - 4096) return n;
+  // multi block: text n + merged planes 10n + output 5n + gt bits; per block symbol: 40 B sort state,
+  // or sa + gap + bwt + rank planes (<= 255 * 32/224 B) while streaming
+  double per_block = 48.0;
+  double rest = avail - 16.3 * (double)n;
+  if (rest <= 0) return 0;
+  long mb = (long)(rest / per_block);
+  mb = std::min(mb, (1L << 31) - 4096);
+  mb = std::min(mb, n);
+  return mb / 32 * 32;
+}
+
+int psc_get_stats(psc_context *ctx, psc_stats *out) {
+  if (!ctx || !out) { set_error("psc_get_stats: null pointer"); return PSC_EARG; }
+  *out = ctx->stats;
+  return PSC_OK;
+}
+
+int psc_construct_sa_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
+                       uint8_t *out_sa5_d) {
+  return guarded([&] {
+    arg_check(ctx && n >= 0 && (n == 0 || (text_d && out_sa5_d)), "psc_construct_sa_d");
+    PSC_CUDA(cudaSetDevice(ctx->device));
+    construct_sa_device(ctx, text_d, n, max_block, out_sa5_d);
+  });
+}
+
+int psc_construct_sa(psc_context *ctx, const uint8_t *text, long n, long max_block, uint8_t *out_sa5) {
+  return guarded([&] {
+    arg_check(ctx && n >= 0 && (n == 0 || (text && out_sa5)), "psc_construct_sa");
+    if (n == 0) return;
+    PSC_CUDA(cudaSetDevice(ctx->device));
+    DevBuf<uint8_t> text_d(ctx, n), out_d(ctx, 5 * (size_t)n);
+    double h2d_ms = 0, d2h_ms = 0;
+    { PhaseTimer t(ctx, &h2d_ms); h2d(ctx, text_d.p, text, n); }
+    construct_sa_device(ctx, text_d.p, n, max_block, out_d.p);
+    { PhaseTimer t(ctx, &d2h_ms); d2h(ctx, out_sa5, out_d.p, 5 * (size_t)n); }
+    sync(ctx);
+    ctx->stats.ms_h2d = h2d_ms;
+    ctx->stats.ms_d2h = d2h_ms;
+  });
+}
+
+}  // extern "C"

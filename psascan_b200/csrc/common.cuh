@@ -1,0 +1,236 @@
+// common.cuh -- context, error handling and device-buffer helpers shared by all kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../include/psascan_cuda.h"
+
+namespace psc {
+
+void set_error(const char *fmt, ...);
+
+struct CudaError { int code; };
+
+#define PSC_CUDA(expr)                                                                  \
+  do {                                                                                  \
+    cudaError_t e__ = (expr);                                                           \
+    if (e__ != cudaSuccess) {                                                           \
+      psc::set_error("%s:%d: %s: %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__)); \
+      throw psc::CudaError{PSC_ECUDA};                                                  \
+    }                                                                                   \
+  } while (0)
+
+#define PSC_LAUNCH_CHECK() PSC_CUDA(cudaGetLastError())
+
+static inline long div_up(long a, long b) { return (a + b - 1) / b; }
+
+}  // namespace psc
+
+struct psc_context {
+  int device = 0;
+  int n_sm = 148;
+  size_t hbm_budget = 0;
+  cudaStream_t stream = nullptr;
+  cudaStream_t side = nullptr;
+  cudaMemPool_t pool = nullptr;
+  psc_stats stats;
+  long launches = 0;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_free;
+};
+
+namespace psc {
+
+// Stream-ordered device buffer (cudaMallocAsync pool: freed blocks are reused without
+// going back to the driver).
+template <typename T>
+struct DevBuf {
+  psc_context *ctx = nullptr;
+  T *p = nullptr;
+  size_t n = 0;
+  DevBuf() {}
+  DevBuf(psc_context *c, size_t count) { alloc(c, count); }
+  DevBuf(const DevBuf &) = delete;
+  DevBuf &operator=(const DevBuf &) = delete;
+  DevBuf(DevBuf &&o) noexcept : ctx(o.ctx), p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+  DevBuf &operator=(DevBuf &&o) noexcept {
+    if (this != &o) { release(); ctx = o.ctx; p = o.p; n = o.n; o.p = nullptr; o.n = 0; }
+    return *this;
+  }
+  void alloc(psc_context *c, size_t count) {
+    release();
+    ctx = c;
+    n = count;
+    size_t bytes = (count ? count : 1) * sizeof(T) + 256;  // slack: kernels may read whole vectors
+    void *q = nullptr;
+    cudaError_t e = cudaMallocAsync(&q, bytes, c->stream);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      set_error("device allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+      throw CudaError{e == cudaErrorMemoryAllocation ? PSC_ENOMEM : PSC_ECUDA};
+    }
+    p = (T *)q;
+  }
+  void zero() { PSC_CUDA(cudaMemsetAsync(p, 0, (n ? n : 1) * sizeof(T) + 256, ctx->stream)); }
+  void release() {
+    if (p) { cudaFreeAsync(p, ctx->stream); p = nullptr; n = 0; }
+  }
+  ~DevBuf() { release(); }
+  operator T *() const { return p; }
+};
+
+// CUDA-event phase timer accumulating into a psc_stats field.
+struct PhaseTimer {
+  psc_context *ctx;
+  double *acc;
+  cudaEvent_t a, b;
+  PhaseTimer(psc_context *c, double *field) : ctx(c), acc(field) {
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEventRecord(a, c->stream);
+  }
+  ~PhaseTimer() {
+    cudaEventRecord(b, ctx->stream);
+    cudaEventSynchronize(b);
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, a, b) == cudaSuccess) *acc += ms;
+    cudaEventDestroy(a); cudaEventDestroy(b);
+  }
+};
+
+template <typename T>
+static inline void h2d(psc_context *ctx, T *dst, const T *src, size_t n) {
+  if (n) PSC_CUDA(cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+}
+template <typename T>
+static inline void d2h(psc_context *ctx, T *dst, const T *src, size_t n) {
+  if (n) PSC_CUDA(cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+}
+static inline void sync(psc_context *ctx) { PSC_CUDA(cudaStreamSynchronize(ctx->stream)); }
+
+#ifdef __CUDACC__
+__device__ __forceinline__ bool bit_get(const uint32_t *bits, long i) {
+  return (bits[i >> 5] >> (i & 31)) & 1u;
+}
+// 4 bytes from any address (little endian); may touch up to 7 bytes past p (buffers have slack)
+__device__ __forceinline__ uint32_t load_u32_any(const uint8_t *p) {
+  uintptr_t a = (uintptr_t)p;
+  const uint32_t *w = (const uint32_t *)(a & ~(uintptr_t)3);
+  uint32_t sh = (uint32_t)(a & 3) * 8;
+  uint32_t w0 = w[0];
+  if (sh == 0) return w0;
+  return __funnelshift_r(w0, w[1], sh);
+}
+// ORs `nvalid` low bits of `word` into a zero-initialised bit array at bit index `bitpos`.
+__device__ __forceinline__ void store_bits_word(uint32_t *bits, long bitpos, uint32_t word, int nvalid) {
+  if (nvalid <= 0) return;
+  if (nvalid < 32) word &= (1u << nvalid) - 1u;
+  int sh = (int)(bitpos & 31);
+  long w = bitpos >> 5;
+  if (sh == 0 && nvalid == 32) { bits[w] = word; return; }
+  if (word << sh) atomicOr(&bits[w], word << sh);
+  if (sh && (word >> (32 - sh))) atomicOr(&bits[w + 1], word >> (32 - sh));
+}
+// length of the common prefix of a[0..lim) and b[0..lim)
+__device__ __forceinline__ long common_prefix(const uint8_t *a, const uint8_t *b, long lim) {
+  long el = 0;
+  while (el < lim) {
+    uint32_t x = load_u32_any(a + el) ^ load_u32_any(b + el);
+    if (x) { el += (__ffs(x) - 1) >> 3; break; }
+    el += 4;
+  }
+  return el > lim ? lim : el;
+}
+#endif
+
+// ---- device-level stage functions (implemented in the .cu files) ------------------------
+
+// radix.cu: LSD onesweep sort of (key64, val32) pairs on the digit list `shifts` (8-bit
+// digits, least significant first).  Result pointers are returned in *keys_out / *vals_out
+// (one of the two buffer pairs).  Passes whose digit is constant over all keys are skipped.
+void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint64_t *keys_b,
+                      uint32_t *vals_b, long n, const int *shifts, int n_shifts,
+                      uint64_t **keys_out, uint32_t **vals_out);
+
+// scan.cu
+void exclusive_scan_u32_to_u64(psc_context *ctx, const uint32_t *in, uint64_t *out, long n,
+                               uint64_t *total_d /* device, may be null */);
+
+// sufsort.cu
+struct BlockSortResult {
+  DevBuf<uint32_t> sa;    // m
+  DevBuf<uint32_t> isa;   // m
+  long i0 = 0;
+};
+// text_d: the block (m symbols, followed in memory by the tail when after_len > 0 is served
+// from the same buffer; `after_d` points at the text right after the block).
+// gt_end_bits_d: forward bit array over block positions p in [0,m): suffix(p) > suffix(end);
+// null when the block is the last one (then every bit is 1).
+void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t *gt_end_bits_d,
+                BlockSortResult *res);
+// gt_end by matching the block against the text after it (K0).
+//   after_d[after_len]  text following the block; after_is_text_end: 1 if it reaches the text end
+//   gt_after_bits_d     forward bits: bit gt_after_off+q (q in [0, after_len)) <-> suffix(end+q+1) > suffix(end)
+void compute_gt_end(psc_context *ctx, const uint8_t *block_d, long m, const uint8_t *after_d,
+                    long after_len, int after_is_text_end, const uint32_t *gt_after_bits_d,
+                    long gt_after_off, uint32_t *gt_end_bits_d);
+// K3: BWT (0 at i0) and forward gt_begin bits: bit p-1 (p in [1,m)) <-> isa[p] > i0.
+void bwt_from_sa(psc_context *ctx, const uint8_t *text_d, const uint32_t *sa_d, long m,
+                 uint8_t *bwt_d);
+void gt_begin_from_isa(psc_context *ctx, const uint32_t *isa_d, long m, uint32_t i0,
+                       uint32_t *bits_d, long bit_off /* bit bit_off+q <-> position q+1, q in [0,m-1);
+                       the array must be zero there */);
+
+// bit-vector layout conversion: forward bits (bit q <-> position lo+q+1) <-> reversed LSB-first
+// bytes with hi = lo + nbits (bit r <-> position hi - r).
+void bits_forward_to_rev(psc_context *ctx, const uint32_t *fwd_d, long nbits, uint8_t *rev_d);
+void bits_rev_to_forward(psc_context *ctx, const uint8_t *rev_d, long nbits, uint32_t *fwd_d);
+
+}  // namespace psc
+
+// rank.cu
+struct psc_rank {
+  long m = 0;
+  long i0 = -1;
+  int n_codes = 0;           // distinct symbols present (placeholder excluded)
+  long n_sectors = 0;        // sectors per symbol
+  int16_t code_of[256];      // -1: absent
+  long counts[256];
+  uint32_t *sectors_d = nullptr;  // [n_codes][n_sectors][8] uint32
+  psc_context *ctx = nullptr;
+};
+
+namespace psc {
+psc_rank *rank_build(psc_context *ctx, const uint8_t *bwt_d, long m, long i0);
+void rank_free(psc_rank *r);
+void rank_query(psc_context *ctx, const psc_rank *r, long nq, const uint64_t *i_d,
+                const uint8_t *c_d, uint64_t *out_d);
+
+// walk.cu
+// K5: ranks of patterns among block suffixes.  after_d = text after the block.
+void initial_ranks(psc_context *ctx, const uint8_t *block_d, const uint32_t *sa_d, long m,
+                   const uint8_t *after_d, long after_len, int after_is_text_end,
+                   const uint32_t *gt_after_bits_d, long gt_after_off, long nstarts,
+                   const uint64_t *starts_d, uint64_t *out_d);
+// K6: LF walk.  Cmap[c] = number of block symbols < c.  gt bits forward over the tail:
+// bit q <-> tail position q+1.
+void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, const uint64_t *Cmap,
+             const uint8_t *tail_d, long t, long nwalk, const uint64_t *walk_beg_d,
+             const uint64_t *start_rank_d, const uint32_t *gt_in_bits_d, long gt_in_off,
+             uint32_t *gt_out_bits_d, long gt_out_off, uint32_t *gap_d);
+
+// merge.cu: planes lo32/hi8 for the running merged SA.
+void merge_level(psc_context *ctx, const uint32_t *sa_d, const uint32_t *gap_d, long m, long beg,
+                 const uint32_t *right_lo, const uint8_t *right_hi, long right_len,
+                 uint32_t *out_lo, uint8_t *out_hi);
+void pack_sa5(psc_context *ctx, const uint32_t *lo, const uint8_t *hi, long n, uint8_t *out5);
+void unpack_sa5(psc_context *ctx, const uint8_t *in5, long n, uint32_t *lo, uint8_t *hi);
+void gap_to_bitvector(psc_context *ctx, const uint32_t *gap_l, long len_l, long len_r,
+                      uint32_t *bv_words);
+void merge_bwt(psc_context *ctx, const uint8_t *bwt_l, const uint8_t *bwt_r, long len_l, long len_r,
+               long i0_l, long i0_r, uint8_t last_l, const uint32_t *bv_words, uint8_t *bwt_out,
+               long *i0_out);
+void split_gap(psc_context *ctx, const uint32_t *bv_words, long len_l, long len_r,
+               const uint32_t *block_gap, uint64_t *left_gap, uint64_t *right_gap);
+}  // namespace psc

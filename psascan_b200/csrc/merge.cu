@@ -1,0 +1,148 @@
+// merge.cu -- stage 4: gap-guided merge as exclusive scan + scatter, and the 40-bit writer.
+//
+// Replaces the single-threaded N-way merge of /root/reference/include/merge.hpp:54-180.  The
+// host cascades right to left: `right` = merged suffixes of everything after the block, and one
+// level places the block's u-th suffix at u + S(u) (S = inclusive scan of the block's gap
+// array) while the entries of `right` fill the other slots in order (same rule as
+// inmem_psascan_src/parallel_merge.hpp:116-154).  The running merged SA is kept as two planes
+// (low 32 bits, high 8 bits); pack_sa5 interleaves them into the reference's uint40 layout
+// (types/uint40.hpp:42-46: uint32 low, uint8 high).
+#include "scan.cuh"
+
+namespace psc {
+
+constexpr int MG_ITEMS = 8;
+constexpr int MG_TILE = SC_THREADS * MG_ITEMS;  // outputs per block
+
+// E[0..m] exclusive scan of gap[0..m];  A(u) = u + E[u] = output slot where run u starts
+// (run u = gap[u] entries of `right`, then the block's u-th suffix when u < m).
+__global__ void __launch_bounds__(SC_THREADS)
+    merge_level_kernel(const uint32_t *__restrict__ sa, const uint64_t *__restrict__ E, long m,
+                       uint64_t beg, const uint32_t *__restrict__ right_lo,
+                       const uint8_t *__restrict__ right_hi, long total,
+                       uint32_t *__restrict__ out_lo, uint8_t *__restrict__ out_hi) {
+  __shared__ uint64_t sA[MG_TILE + 2];
+  __shared__ long s_u0;
+  const long q0 = (long)blockIdx.x * MG_TILE;
+  if (threadIdx.x == 0) {
+    // largest u in [0, m] with u + E[u] <= q0
+    long lo = 0, hi = m;
+    while (lo < hi) {
+      long mid = (lo + hi + 1) >> 1;
+      if ((uint64_t)mid + E[mid] <= (uint64_t)q0) lo = mid; else hi = mid - 1;
+    }
+    s_u0 = lo;
+  }
+  __syncthreads();
+  const long u0 = s_u0;
+  const long cnt = min((long)MG_TILE + 2, m + 1 - u0);  // A(u0 .. u0+cnt-1)
+  for (long e = threadIdx.x; e < cnt; e += SC_THREADS) sA[e] = (uint64_t)(u0 + e) + E[u0 + e];
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < MG_ITEMS; ++k) {
+    long q = q0 + threadIdx.x + (long)k * SC_THREADS;
+    if (q >= total) break;
+    // largest e in [0, cnt) with sA[e] <= q
+    long lo = 0, hi = min(cnt - 1, q - q0 + 0L);
+    // A(u0 + e) >= q0 + e is not guaranteed for e = 0 only (A(u0) <= q0), so hi = q - q0 is safe
+    while (lo < hi) {
+      long mid = (lo + hi + 1) >> 1;
+      if (sA[mid] <= (uint64_t)q) lo = mid; else hi = mid - 1;
+    }
+    long u = u0 + lo;
+    uint64_t v;
+    if (u < m && lo + 1 < cnt && sA[lo + 1] - 1 == (uint64_t)q) {
+      v = beg + sa[u];
+    } else {
+      uint64_t r = (uint64_t)(q - u);  // u block suffixes precede slot q, the rest come from `right`
+      v = (uint64_t)right_lo[r] | ((uint64_t)right_hi[r] << 32);
+    }
+    out_lo[q] = (uint32_t)v;
+    out_hi[q] = (uint8_t)(v >> 32);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    sa_to_planes_kernel(const uint32_t *__restrict__ sa, long m, uint64_t beg,
+                        uint32_t *__restrict__ lo, uint8_t *__restrict__ hi) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  uint64_t v = beg + sa[i];
+  lo[i] = (uint32_t)v;
+  hi[i] = (uint8_t)(v >> 32);
+}
+
+void merge_level(psc_context *ctx, const uint32_t *sa_d, const uint32_t *gap_d, long m, long beg,
+                 const uint32_t *right_lo, const uint8_t *right_hi, long right_len,
+                 uint32_t *out_lo, uint8_t *out_hi) {
+  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
+  long total = m + right_len;
+  if (total == 0) return;
+  if (right_len == 0) {
+    sa_to_planes_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(sa_d, m, (uint64_t)beg, out_lo, out_hi);
+    PSC_LAUNCH_CHECK();
+    ctx->launches++;
+    return;
+  }
+  DevBuf<uint64_t> E(ctx, m + 1);
+  exclusive_scan_u32_to_u64(ctx, gap_d, E.p, m + 1, nullptr);
+  merge_level_kernel<<<(unsigned)div_up(total, MG_TILE), SC_THREADS, 0, ctx->stream>>>(
+      sa_d, E.p, m, (uint64_t)beg, right_lo, right_hi, total, out_lo, out_hi);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+}
+
+// ---- 40-bit writer: 4 entries = 20 bytes = 5 aligned words per thread --------------------------
+__global__ void __launch_bounds__(256)
+    pack_sa5_kernel(const uint32_t *__restrict__ lo, const uint8_t *__restrict__ hi, long n,
+                    uint32_t *out_words, uint8_t *out_bytes) {
+  long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  long i = g * 4;
+  if (i >= n) return;
+  if (i + 4 <= n) {
+    uint4 l = *reinterpret_cast<const uint4 *>(lo + i);
+    uint32_t h = *reinterpret_cast<const uint32_t *>(hi + i);
+    uint32_t h0 = h & 255, h1 = (h >> 8) & 255, h2 = (h >> 16) & 255, h3 = h >> 24;
+    uint32_t *o = out_words + g * 5;
+    o[0] = l.x;
+    o[1] = h0 | (l.y << 8);
+    o[2] = (l.y >> 24) | (h1 << 8) | (l.z << 16);
+    o[3] = (l.z >> 16) | (h2 << 16) | (l.w << 24);
+    o[4] = (l.w >> 8) | (h3 << 24);
+  } else {
+    for (long k = i; k < n; ++k) {
+      uint32_t l = lo[k];
+      uint8_t *o = out_bytes + k * 5;
+      o[0] = (uint8_t)l; o[1] = (uint8_t)(l >> 8); o[2] = (uint8_t)(l >> 16); o[3] = (uint8_t)(l >> 24);
+      o[4] = hi[k];
+    }
+  }
+}
+
+void pack_sa5(psc_context *ctx, const uint32_t *lo, const uint8_t *hi, long n, uint8_t *out5) {
+  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
+  if (n <= 0) return;
+  pack_sa5_kernel<<<(unsigned)div_up(div_up(n, 4), 256), 256, 0, ctx->stream>>>(
+      lo, hi, n, reinterpret_cast<uint32_t *>(out5), out5);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+}
+
+__global__ void __launch_bounds__(256)
+    unpack_sa5_kernel(const uint8_t *__restrict__ in5, long n, uint32_t *__restrict__ lo,
+                      uint8_t *__restrict__ hi) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint8_t *p = in5 + i * 5;
+  lo[i] = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+  hi[i] = p[4];
+}
+
+void unpack_sa5(psc_context *ctx, const uint8_t *in5, long n, uint32_t *lo, uint8_t *hi) {
+  if (n <= 0) return;
+  unpack_sa5_kernel<<<(unsigned)div_up(n, 256), 256, 0, ctx->stream>>>(in5, n, lo, hi);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+}
+
+}  // namespace psc

@@ -1,0 +1,404 @@
+// sufsort.cu -- stage 1: block suffix sort by prefix doubling over packed 64-bit keys.
+//
+// Replaces inmem_psascan<saidx_t,12>() (inmem_psascan_src/inmem_psascan.hpp:64-304) and the
+// vendored sorter behind it (initial_partial_sufsort.hpp:272-289).  What is kept from the
+// reference is the *renaming* that makes a plain suffix sort of the block equal to whole-text
+// order (initial_partial_sufsort.hpp:61-80): the block's last symbol, every symbol greater
+// than it, and every occurrence of it that is followed by a suffix greater than suffix(end)
+// (the gt_end bit) move up by one.  Everything else is new:
+//   round 0   key = the first k renamed symbols packed at b bits each (k*b <= 64), LSD radix
+//             sort of (key, position)
+//   round r   only suffixes still sharing their key stay "active"; key = (group head << 32 |
+//             ISA[pos + h] + 1), sorted again, h doubles.
+#include <algorithm>
+#include "scan.cuh"
+
+namespace psc {
+
+constexpr int PD_ITEMS = 8;
+constexpr int PD_TILE = SC_THREADS * PD_ITEMS;
+
+
+// ---- symbol statistics ---------------------------------------------------------------------
+// hist[c] for c in 0..255, hist[256] = number of positions with text[i] == last that are NOT
+// incremented by the renaming (i < m-1 and gt_end[i+1] == 0).
+__global__ void __launch_bounds__(256)
+    symbol_hist_kernel(const uint8_t *__restrict__ text, long m, const uint32_t *__restrict__ gt_end,
+                       int last, unsigned long long *__restrict__ hist) {
+  __shared__ uint32_t sh[257];
+  for (int i = threadIdx.x; i < 257; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  long stride = (long)gridDim.x * blockDim.x;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += stride) {
+    int c = text[i];
+    atomicAdd(&sh[c], 1u);
+    if (c == last && i < m - 1 && gt_end != nullptr && !bit_get(gt_end, i + 1)) atomicAdd(&sh[256], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 257; i += blockDim.x)
+    if (sh[i]) atomicAdd(&hist[i], (unsigned long long)sh[i]);
+}
+
+struct RenameLut {
+  uint16_t code[256];  // dense code (1..sigma') of the renamed symbol; for c == last: the LOW code
+  uint16_t code_last_high;
+  int last;
+  int bits;  // bits per code
+  int k;     // symbols per key
+};
+
+// ---- round 0 keys --------------------------------------------------------------------------
+__global__ void __launch_bounds__(SC_THREADS)
+    init_keys_kernel(const uint8_t *__restrict__ text, long m, const uint32_t *__restrict__ gt_end,
+                     RenameLut lut, uint64_t *__restrict__ keys, uint32_t *__restrict__ idx) {
+  extern __shared__ uint16_t codes[];  // PD_TILE + k
+  const long t0 = (long)blockIdx.x * PD_TILE;
+  const int span = PD_TILE + lut.k;
+  for (int e = threadIdx.x; e < span; e += SC_THREADS) {
+    long i = t0 + e;
+    uint16_t cd = 0;
+    if (i < m) {
+      int c = text[i];
+      cd = lut.code[c];
+      if (c == lut.last && (i == m - 1 || gt_end == nullptr || bit_get(gt_end, i + 1)))
+        cd = lut.code_last_high;
+    }
+    codes[e] = cd;
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < PD_TILE; e += SC_THREADS) {
+    long i = t0 + e;
+    if (i >= m) break;
+    uint64_t key = 0;
+    for (int s = 0; s < lut.k; ++s) key = (key << lut.bits) | codes[e + s];
+    keys[i] = key;
+    idx[i] = (uint32_t)i;
+  }
+}
+
+// ---- grouping after a sort ------------------------------------------------------------------
+// K[0..n) sorted keys.  head(i) = K[i] != K[i-1];  an element is "active" unless it is alone
+// in its group.  Tile aggregates: number of active elements, index+1 of the last head.
+__global__ void __launch_bounds__(SC_THREADS)
+    group_reduce_kernel(const uint64_t *__restrict__ K, long n, uint64_t *__restrict__ agg_act,
+                        uint64_t *__restrict__ agg_head) {
+  __shared__ uint64_t sm[SC_THREADS / 32 + 1];
+  const long base = (long)blockIdx.x * PD_TILE + (long)threadIdx.x * PD_ITEMS;
+  uint64_t prev = (base > 0 && base - 1 < n) ? K[base - 1] : 0;
+  uint64_t cur = base < n ? K[base] : 0;
+  uint64_t n_act = 0, last_head = 0;
+#pragma unroll
+  for (int k = 0; k < PD_ITEMS; ++k) {
+    long i = base + k;
+    uint64_t nxt = (i + 1 < n) ? K[i + 1] : 0;
+    if (i < n) {
+      bool head = (i == 0) || (cur != prev);
+      bool head_next = (i == n - 1) || (nxt != cur);
+      if (head) last_head = (uint64_t)i + 1;
+      if (!(head && head_next)) ++n_act;
+    }
+    prev = cur;
+    cur = nxt;
+  }
+  uint64_t tot_act, tot_head;
+  block_excl_sum<uint64_t>(n_act, sm, &tot_act);
+  block_excl_max<uint64_t>(last_head, sm, &tot_head);
+  if (threadIdx.x == 0) { agg_act[blockIdx.x] = tot_act; agg_head[blockIdx.x] = tot_head; }
+}
+
+// Applies one round: writes SA and ISA for the sorted elements and compacts the still-active
+// ones into (keyY = new group head << 32, valY = text position, posY = SA slot).
+//   pos == nullptr: element j sits in SA slot j (round 0).
+__global__ void __launch_bounds__(SC_THREADS)
+    group_apply_kernel(const uint64_t *__restrict__ K, const uint32_t *__restrict__ V,
+                       const uint32_t *__restrict__ pos, long n,
+                       const uint64_t *__restrict__ agg_act, const uint64_t *__restrict__ agg_head,
+                       uint32_t *__restrict__ sa, uint32_t *__restrict__ isa,
+                       uint64_t *__restrict__ keyY, uint32_t *__restrict__ valY,
+                       uint32_t *__restrict__ posY) {
+  __shared__ uint64_t sm[SC_THREADS / 32 + 1];
+  const long base = (long)blockIdx.x * PD_TILE + (long)threadIdx.x * PD_ITEMS;
+  bool head[PD_ITEMS], act[PD_ITEMS];
+  uint64_t prev = (base > 0 && base - 1 < n) ? K[base - 1] : 0;
+  uint64_t cur = base < n ? K[base] : 0;
+  uint64_t n_act = 0, last_head = 0;
+#pragma unroll
+  for (int k = 0; k < PD_ITEMS; ++k) {
+    long i = base + k;
+    uint64_t nxt = (i + 1 < n) ? K[i + 1] : 0;
+    head[k] = false;
+    act[k] = false;
+    if (i < n) {
+      head[k] = (i == 0) || (cur != prev);
+      bool head_next = (i == n - 1) || (nxt != cur);
+      if (head[k]) last_head = (uint64_t)i + 1;
+      act[k] = !(head[k] && head_next);
+      if (act[k]) ++n_act;
+    }
+    prev = cur;
+    cur = nxt;
+  }
+  uint64_t tot;
+  uint64_t act_off = block_excl_sum<uint64_t>(n_act, sm, &tot) + agg_act[blockIdx.x];
+  uint64_t hd = max(block_excl_max<uint64_t>(last_head, sm, &tot), agg_head[blockIdx.x]);
+  uint32_t hp = 0;
+  bool hp_valid = false;
+#pragma unroll
+  for (int k = 0; k < PD_ITEMS; ++k) {
+    long i = base + k;
+    if (i >= n) break;
+    if (head[k]) { hd = (uint64_t)i + 1; hp_valid = false; }
+    if (!hp_valid) { hp = pos ? pos[hd - 1] : (uint32_t)(hd - 1); hp_valid = true; }
+    uint32_t v = V[i];
+    uint32_t slot = pos ? pos[i] : (uint32_t)i;
+    sa[slot] = v;
+    isa[v] = hp;
+    if (act[k]) {
+      keyY[act_off] = (uint64_t)hp << 32;
+      valY[act_off] = v;
+      posY[act_off] = slot;
+      ++act_off;
+    }
+  }
+}
+
+// second half of the next key: ISA[position + h] + 1, 0 when past the block end
+__global__ void __launch_bounds__(256)
+    second_key_kernel(uint64_t *__restrict__ keyY, const uint32_t *__restrict__ valY, long a,
+                      const uint32_t *__restrict__ isa, long m, long h) {
+  long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= a) return;
+  long p = (long)valY[j] + h;
+  uint32_t r = p < m ? isa[p] + 1u : 0u;
+  keyY[j] |= (uint64_t)r;
+}
+
+static int bits_for(uint64_t v) { int b = 0; while (v) { ++b; v >>= 1; } return b; }
+
+// ---- host driver ------------------------------------------------------------------------------
+void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t *gt_end_bits_d,
+                BlockSortResult *res) {
+  PhaseTimer timer(ctx, &ctx->stats.ms_sort);
+  res->sa.alloc(ctx, m);
+  res->isa.alloc(ctx, m);
+  if (m == 0) return;
+  uint8_t last = 0;
+  PSC_CUDA(cudaMemcpyAsync(&last, text_d + m - 1, 1, cudaMemcpyDeviceToHost, ctx->stream));
+  sync(ctx);
+
+  // symbol statistics -> dense codes of the renamed alphabet
+  DevBuf<unsigned long long> hist_d(ctx, 257);
+  hist_d.zero();
+  int hb = (int)std::min<long>(div_up(m, 256 * 16), (long)ctx->n_sm * 8);
+  symbol_hist_kernel<<<hb, 256, 0, ctx->stream>>>(text_d, m, gt_end_bits_d, last, hist_d.p);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+  unsigned long long hist[257];
+  d2h(ctx, hist, hist_d.p, 257);
+  sync(ctx);
+  if (hist[255] != 0) { set_error("byte 255 in the text"); throw CudaError{PSC_ESENTINEL}; }
+  RenameLut lut;
+  memset(&lut, 0, sizeof(lut));
+  lut.last = last;
+  double p2 = 0;
+  int sigma = 0;
+  for (int c = 0; c < 256; ++c) {
+    if (c == last) {
+      unsigned long long low = hist[256], high = hist[c] - low;
+      if (low) { lut.code[c] = (uint16_t)++sigma; p2 += ((double)low / m) * ((double)low / m); }
+      lut.code_last_high = (uint16_t)++sigma;  // position m-1 always takes it
+      p2 += ((double)high / m) * ((double)high / m);
+    } else if (hist[c]) {
+      lut.code[c] = (uint16_t)++sigma;
+      p2 += ((double)hist[c] / m) * ((double)hist[c] / m);
+    }
+  }
+  lut.bits = bits_for((uint64_t)sigma);
+  int kmax = 64 / lut.bits;
+  // smallest k with m * p2^k <= 1/16 (expected share of suffixes still tied after round 0)
+  int k = 1;
+  {
+    double v = (double)m * 16.0;
+    while (k < kmax && v * p2 > 1.0) { v *= p2; ++k; }
+    if (v * p2 > 1.0) k = kmax;
+  }
+  int passes = (k * lut.bits + 7) / 8;
+  k = std::min(kmax, (passes * 8) / lut.bits);  // fill the last digit
+  if (k > m) k = (int)std::max<long>(1, m);
+  passes = (k * lut.bits + 7) / 8;
+  lut.k = k;
+
+  DevBuf<uint64_t> keyA(ctx, m), keyB(ctx, m);
+  DevBuf<uint32_t> valA(ctx, m), valB(ctx, m);
+  long tiles = div_up(m, PD_TILE);
+  init_keys_kernel<<<(unsigned)tiles, SC_THREADS, (PD_TILE + k) * sizeof(uint16_t), ctx->stream>>>(
+      text_d, m, gt_end_bits_d, lut, keyA.p, valA.p);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+
+  int shifts[8];
+  for (int p = 0; p < passes; ++p) shifts[p] = 8 * p;
+  uint64_t *K; uint32_t *V;
+  radix_sort_pairs(ctx, keyA.p, valA.p, keyB.p, valB.p, m, shifts, passes, &K, &V);
+
+  DevBuf<uint32_t> posA, posB;
+  uint32_t *pos = nullptr;  // round 0: identity
+  long a = m;
+  long h = k;
+  DevBuf<uint64_t> total_d(ctx, 1);
+  const int lowb = bits_for((uint64_t)m), highb = bits_for((uint64_t)(m > 1 ? m - 1 : 1));
+  for (int round = 0;; ++round) {
+    long t = div_up(a, PD_TILE);
+    DevBuf<uint64_t> agg_act(ctx, t), agg_head(ctx, t);
+    group_reduce_kernel<<<(unsigned)t, SC_THREADS, 0, ctx->stream>>>(K, a, agg_act.p, agg_head.p);
+    PSC_LAUNCH_CHECK();
+    scan_aggregates_sum(ctx, agg_act.p, t, total_d.p);
+    scan_aggregates_max(ctx, agg_head.p, t);
+    uint64_t na = 0;
+    d2h(ctx, &na, total_d.p, 1);
+    sync(ctx);
+    // outputs of the compaction go to the buffer pair the sort result is NOT in
+    uint64_t *KY = (K == keyA.p) ? keyB.p : keyA.p;
+    uint32_t *VY = (V == valA.p) ? valB.p : valA.p;
+    DevBuf<uint32_t> &posY = (pos == posA.p && pos != nullptr) ? posB : posA;
+    posY.alloc(ctx, na);
+    group_apply_kernel<<<(unsigned)t, SC_THREADS, 0, ctx->stream>>>(
+        K, V, pos, a, agg_act.p, agg_head.p, res->sa.p, res->isa.p, KY, VY, posY.p);
+    PSC_LAUNCH_CHECK();
+    ctx->launches += 2;
+    ctx->stats.doubling_rounds++;
+    if (na == 0) break;
+    a = (long)na;
+    second_key_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, res->isa.p, m, h);
+    PSC_LAUNCH_CHECK();
+    ctx->launches++;
+    pos = posY.p;
+    int nsh = 0;
+    for (int b = 0; b < lowb; b += 8) shifts[nsh++] = b;
+    for (int b = 0; b < highb; b += 8) shifts[nsh++] = 32 + b;
+    uint64_t *KO = (KY == keyA.p) ? keyB.p : keyA.p;
+    uint32_t *VO = (VY == valA.p) ? valB.p : valA.p;
+    radix_sort_pairs(ctx, KY, VY, KO, VO, a, shifts, nsh, &K, &V);
+    h *= 2;
+  }
+  uint32_t i0 = 0;
+  d2h(ctx, &i0, res->isa.p, 1);
+  sync(ctx);
+  res->i0 = i0;
+}
+
+// ---- K0: gt_end by matching the block against the text after it -------------------------------
+// compute_initial_gt_bitvectors.hpp:61-148 (semantics; brute force with 4-byte compares, the
+// reference's ms-decomposition speed-up is not reproduced).
+__global__ void __launch_bounds__(256)
+    gt_end_kernel(const uint8_t *__restrict__ block, long m, const uint8_t *__restrict__ after,
+                  long after_len, int after_is_text_end, const uint32_t *__restrict__ gt_after,
+                  long gt_after_off, uint32_t *__restrict__ out_bits) {
+  long p = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  bool g = false;
+  if (p < m) {
+    long lim = min(m - p, after_len);
+    long el = common_prefix(block + p, after, lim);
+    if (el == after_len && after_is_text_end) g = true;
+    else if (p + el == m) g = !bit_get(gt_after, gt_after_off + el - 1);
+    else g = block[p + el] > after[el];
+  }
+  uint32_t word = __ballot_sync(0xffffffffu, g);
+  if ((threadIdx.x & 31) == 0 && (p < m)) out_bits[p >> 5] = word;
+}
+
+void compute_gt_end(psc_context *ctx, const uint8_t *block_d, long m, const uint8_t *after_d,
+                    long after_len, int after_is_text_end, const uint32_t *gt_after_bits_d,
+                    long gt_after_off, uint32_t *gt_end_bits_d) {
+  PhaseTimer timer(ctx, &ctx->stats.ms_gt_end);
+  if (m == 0) return;
+  gt_end_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(
+      block_d, m, after_d, after_len, after_is_text_end, gt_after_bits_d, gt_after_off, gt_end_bits_d);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+}
+
+// ---- K3: BWT and gt_begin ------------------------------------------------------------------------
+// inmem_bwt_from_sa.hpp:48-56 and change_gt_reference_point.hpp:62-118
+__global__ void __launch_bounds__(256)
+    bwt_kernel(const uint8_t *__restrict__ text, const uint32_t *__restrict__ sa, long m,
+               uint8_t *__restrict__ bwt) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  uint32_t s = sa[i];
+  bwt[i] = s ? text[s - 1] : (uint8_t)0;
+}
+
+void bwt_from_sa(psc_context *ctx, const uint8_t *text_d, const uint32_t *sa_d, long m,
+                 uint8_t *bwt_d) {
+  PhaseTimer timer(ctx, &ctx->stats.ms_bwt);
+  if (m == 0) return;
+  bwt_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(text_d, sa_d, m, bwt_d);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+}
+
+// bit bit_off+q <-> block position q+1 (q+1 < m): isa[q+1] > i0.
+__global__ void __launch_bounds__(256)
+    gt_begin_kernel(const uint32_t *__restrict__ isa, long m, uint32_t i0, uint32_t *__restrict__ bits,
+                    long bit_off) {
+  long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  bool g = (q + 1 < m) && (isa[q + 1] > i0);
+  uint32_t word = __ballot_sync(0xffffffffu, g);
+  if ((threadIdx.x & 31) == 0) {
+    long rem = (m - 1) - q;
+    store_bits_word(bits, bit_off + q, word, rem >= 32 ? 32 : (int)rem);
+  }
+}
+
+void gt_begin_from_isa(psc_context *ctx, const uint32_t *isa_d, long m, uint32_t i0,
+                       uint32_t *bits_d, long bit_off) {
+  PhaseTimer timer(ctx, &ctx->stats.ms_bwt);
+  if (m <= 1) return;
+  gt_begin_kernel<<<(unsigned)div_up(m - 1, 256), 256, 0, ctx->stream>>>(isa_d, m, i0, bits_d, bit_off);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+}
+
+// ---- bit-vector layout conversion (bitvector.hpp:61-67, multifile.hpp:57-68) -----------------------
+__global__ void bits_fwd_to_rev_kernel(const uint32_t *__restrict__ fwd, long nbits,
+                                       uint8_t *__restrict__ rev) {
+  long b = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= (nbits + 7) / 8) return;
+  uint32_t byte = 0;
+  for (int k = 0; k < 8; ++k) {
+    long r = b * 8 + k;
+    if (r < nbits && bit_get(fwd, nbits - 1 - r)) byte |= 1u << k;
+  }
+  rev[b] = (uint8_t)byte;
+}
+__global__ void bits_rev_to_fwd_kernel(const uint8_t *__restrict__ rev, long nbits,
+                                       uint32_t *__restrict__ fwd) {
+  long w = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= (nbits + 31) / 32) return;
+  uint32_t word = 0;
+  for (int k = 0; k < 32; ++k) {
+    long q = w * 32 + k;
+    if (q < nbits) {
+      long r = nbits - 1 - q;
+      if ((rev[r >> 3] >> (r & 7)) & 1) word |= 1u << k;
+    }
+  }
+  fwd[w] = word;
+}
+void bits_forward_to_rev(psc_context *ctx, const uint32_t *fwd_d, long nbits, uint8_t *rev_d) {
+  long nb = (nbits + 7) / 8;
+  if (!nb) return;
+  bits_fwd_to_rev_kernel<<<(unsigned)div_up(nb, 256), 256, 0, ctx->stream>>>(fwd_d, nbits, rev_d);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+}
+void bits_rev_to_forward(psc_context *ctx, const uint8_t *rev_d, long nbits, uint32_t *fwd_d) {
+  long nw = (nbits + 31) / 32;
+  if (!nw) return;
+  bits_rev_to_fwd_kernel<<<(unsigned)div_up(nw, 256), 256, 0, ctx->stream>>>(rev_d, nbits, fwd_d);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+}
+
+}  // namespace psc

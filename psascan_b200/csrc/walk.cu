@@ -1,0 +1,157 @@
+// walk.cu -- stage 2 (initial ranks) and stage 3b (the LF walk / gap computation).
+//
+// K5 replaces em_compute_initial_ranks() (/root/reference/include/em_compute_initial_ranks.hpp:
+// 222-319, 513-561): one thread per walker start binary-searches the block SA; a block suffix
+// that runs into the block end is decided by the tail's gt bit exactly like lcp_compare()
+// (:54-76), so every rank is exact and independent (no right-to-left tie chain, :285-310).
+//
+// K6 replaces parallel_stream() + gap_parallel_updater (stream.hpp:147-158, update.hpp:86-96,
+// compute_gap.hpp:77-85): one walker per thread, thousands per SM, each doing the dependent
+// chain i <- C[c] + occ(c, i) (+1) with one 32-byte sector read per step and a RED on the
+// uint32 gap counter (optionally warp-aggregated through match.any).
+#include "rank.cuh"
+
+namespace psc {
+
+// ---- K5 ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+    initial_ranks_kernel(const uint8_t *__restrict__ block, const uint32_t *__restrict__ sa, long m,
+                         const uint8_t *__restrict__ after, long after_len, int after_is_text_end,
+                         const uint32_t *__restrict__ gt_after, long gt_after_off, long nstarts,
+                         const uint64_t *__restrict__ starts, uint64_t *__restrict__ out) {
+  long k = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nstarts) return;
+  long st = (long)starts[k];
+  long plen = after_len - st;
+  if (plen <= 0 && after_is_text_end) { out[k] = 0; return; }  // :175-178 empty suffix
+  const uint8_t *pat = after + st;
+  long left = 0, right = m;
+  while (left != right) {
+    long mid = (left + right) >> 1;
+    long s = sa[mid];
+    long slen = m - s;
+    long lim = slen < plen ? slen : plen;
+    long lcp = common_prefix(block + s, pat, lim);
+    bool pat_greater;
+    if (lcp == slen) pat_greater = bit_get(gt_after, gt_after_off + st + slen - 1);  // :66-68
+    else if (lcp == plen) pat_greater = false;                                       // :69-71
+    else pat_greater = pat[lcp] > block[s + lcp];                                    // :72-75
+    if (pat_greater) left = mid + 1; else right = mid;
+  }
+  out[k] = (uint64_t)left;
+}
+
+void initial_ranks(psc_context *ctx, const uint8_t *block_d, const uint32_t *sa_d, long m,
+                   const uint8_t *after_d, long after_len, int after_is_text_end,
+                   const uint32_t *gt_after_bits_d, long gt_after_off, long nstarts,
+                   const uint64_t *starts_d, uint64_t *out_d) {
+  PhaseTimer timer(ctx, &ctx->stats.ms_init_ranks);
+  if (nstarts <= 0) return;
+  initial_ranks_kernel<<<(unsigned)div_up(nstarts, 128), 128, 0, ctx->stream>>>(
+      block_d, sa_d, m, after_d, after_len, after_is_text_end, gt_after_bits_d, gt_after_off, nstarts,
+      starts_d, out_d);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+}
+
+// ---- K6 ---------------------------------------------------------------------------------------
+struct WalkTables {
+  uint32_t C[256];     // number of block symbols smaller than c  (compute_gap.hpp:77-85)
+  int16_t code[256];   // dense code in the rank structure, -1 = symbol absent from the BWT
+};
+
+template <bool AGG>
+__global__ void __launch_bounds__(256)
+    lf_walk_kernel(RankView rv, uint32_t i0, int last, const WalkTables *__restrict__ tables,
+                   const uint8_t *__restrict__ tail, long nwalk, const uint64_t *__restrict__ walk_beg,
+                   const uint64_t *__restrict__ start_rank, const uint32_t *__restrict__ gt_in,
+                   long gt_in_off, uint32_t *__restrict__ gt_out, long gt_out_off,
+                   uint32_t *__restrict__ gap) {
+  __shared__ uint32_t sC[256];
+  __shared__ int16_t sCode[256];
+  sC[threadIdx.x] = tables->C[threadIdx.x];
+  sCode[threadIdx.x] = tables->code[threadIdx.x];
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  long w = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  long s = 0, e = 0;
+  uint32_t i = 0;
+  if (w < nwalk) { s = (long)walk_beg[w]; e = (long)walk_beg[w + 1]; i = (uint32_t)start_rank[w]; }
+  long steps = e - s, max_steps = steps;
+#pragma unroll
+  for (int o = 16; o; o >>= 1) max_steps = max(max_steps, __shfl_xor_sync(0xffffffffu, max_steps, o));
+
+  long j = e;                      // suffix tail+j is the one whose rank `i` currently holds
+  uintptr_t cur_chunk = ~(uintptr_t)0;
+  uint4 tb = make_uint4(0, 0, 0, 0);
+  long cur_in_w = -1, cur_out_w = -1;
+  uint32_t in_word = 0, out_word = 0;
+  for (long k = 0; k < max_steps; ++k) {
+    const bool active = k < steps;
+    if (active) {
+      // symbol tail[j-1]
+      uintptr_t a = (uintptr_t)(tail + j - 1);
+      uintptr_t ch = a & ~(uintptr_t)15;
+      if (ch != cur_chunk) { tb = *reinterpret_cast<const uint4 *>(ch); cur_chunk = ch; }
+      uint32_t b = (uint32_t)(a & 15);
+      uint32_t word = (b & 8) ? ((b & 4) ? tb.w : tb.z) : ((b & 4) ? tb.y : tb.x);
+      int c = (int)((word >> ((b & 3) * 8)) & 255u);
+      // gt bits of suffix j: new one out (stream.hpp:150), old one in (:151)
+      long ob = gt_out_off + j - 1;
+      if (gt_out) {
+        if ((ob >> 5) != cur_out_w) {
+          if (cur_out_w >= 0 && out_word) atomicOr(&gt_out[cur_out_w], out_word);
+          cur_out_w = ob >> 5;
+          out_word = 0;
+        }
+        if (i > i0) out_word |= 1u << (ob & 31);
+      }
+      long ib = gt_in_off + j - 1;
+      if ((ib >> 5) != cur_in_w) { cur_in_w = ib >> 5; in_word = gt_in ? gt_in[cur_in_w] : 0u; }
+      uint32_t gin = (in_word >> (ib & 31)) & 1u;
+      // LF step (:153-155; no delta: the placeholder has no bit in any plane)
+      int code = sCode[c];
+      uint32_t occ = code >= 0 ? rank_occ(rv, code, i) : 0u;
+      i = sC[c] + occ + ((c == last) ? gin : 0u);
+      --j;
+    }
+    if (AGG) {
+      uint32_t peers = __match_any_sync(0xffffffffu, active ? i : (0xffffffffu - lane));
+      if (active && lane == __ffs(peers) - 1) atomicAdd(&gap[i], (uint32_t)__popc(peers));
+    } else {
+      if (active) atomicAdd(&gap[i], 1u);
+    }
+  }
+  if (gt_out && cur_out_w >= 0 && out_word) atomicOr(&gt_out[cur_out_w], out_word);
+}
+
+void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, const uint64_t *Cmap,
+             const uint8_t *tail_d, long t, long nwalk, const uint64_t *walk_beg_d,
+             const uint64_t *start_rank_d, const uint32_t *gt_in_bits_d, long gt_in_off,
+             uint32_t *gt_out_bits_d, long gt_out_off, uint32_t *gap_d) {
+  PhaseTimer timer(ctx, &ctx->stats.ms_walk);
+  if (nwalk <= 0 || t <= 0) return;
+  WalkTables tb;
+  for (int c = 0; c < 256; ++c) { tb.C[c] = (uint32_t)Cmap[c]; tb.code[c] = r->code_of[c]; }
+  DevBuf<WalkTables> tb_d(ctx, 1);
+  h2d(ctx, tb_d.p, &tb, 1);
+  RankView rv{r->sectors_d, r->n_sectors, (uint32_t)r->m};
+  static int agg = -1;
+  if (agg < 0) { const char *e = getenv("PSC_WALK_AGG"); agg = e ? atoi(e) : 0; }
+  unsigned blocks = (unsigned)div_up(nwalk, 256);
+  if (agg)
+    lf_walk_kernel<true><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d,
+                                                           start_rank_d, gt_in_bits_d, gt_in_off,
+                                                           gt_out_bits_d, gt_out_off, gap_d);
+  else
+    lf_walk_kernel<false><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d,
+                                                            start_rank_d, gt_in_bits_d, gt_in_off,
+                                                            gt_out_bits_d, gt_out_off, gap_d);
+  PSC_LAUNCH_CHECK();
+  sync(ctx);  // tb is a stack object
+  ctx->launches++;
+  ctx->stats.lf_steps += t;
+  ctx->stats.walkers = nwalk;
+}
+
+}  // namespace psc
