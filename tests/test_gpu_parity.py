@@ -1,0 +1,209 @@
+"""GPU parity tests (run on the B200 box): every stage of the CUDA path, called through the C ABI
+(psascan_b200.lib -> libpsascan_cuda.so), against the CPU oracle on the same seeded inputs, and the
+whole path against the reference's golden .sa5 files.  Integer work: bit-exact."""
+import numpy as np
+import pytest
+import oracle_lib as O
+from golden_cases import golden_cases, golden_text
+from psascan_b200 import textgen
+from psascan_b200.lib import decode_sa5
+
+pytestmark = pytest.mark.gpu
+CASES = golden_cases()
+
+
+def rev_bits(flags_by_pos, n, lo, hi):
+    return O.pack_gt_rev(flags_by_pos, n, lo, hi)
+
+
+def texts_small():
+    rng = np.random.default_rng(123)
+    out = [("one", np.array([7], dtype=np.uint8)), ("two_eq", np.array([3, 3], dtype=np.uint8)),
+           ("all_a", np.full(1000, 97, dtype=np.uint8)), ("zeros", np.zeros(777, dtype=np.uint8)),
+           ("ab_period", np.tile(np.array([0, 1], dtype=np.uint8), 2500)),
+           ("dna", textgen.dna(30000, seed=5)), ("rand255", textgen.random_bytes(50000, seed=6)),
+           ("markov", textgen.markov(40000, seed=8)),
+           ("rep", textgen.repetitive(60000, seed=4, seed_len=3000, rate=1e-3)),
+           ("periodic0", textgen.periodic(20000, period=97, sigma=3)),
+           ("tiny_rand", rng.integers(0, 3, size=257, dtype=np.uint8))]
+    return out
+
+
+@pytest.mark.parametrize("name,text", texts_small(), ids=[t[0] for t in texts_small()])
+def test_construct_sa_single_block(ctx, name, text):
+    got = decode_sa5(ctx.construct_sa(text))
+    assert np.array_equal(got, O.sa(text))
+
+
+@pytest.mark.parametrize("name,text", texts_small(), ids=[t[0] for t in texts_small()])
+@pytest.mark.parametrize("nblk", [2, 3, 7])
+def test_construct_sa_multi_block(ctx, name, text, nblk):
+    n = len(text)
+    mb = max(1, -(-n // nblk))
+    got = decode_sa5(ctx.construct_sa(text, max_block=mb))
+    assert np.array_equal(got, O.sa(text)), (name, mb)
+
+
+@pytest.mark.parametrize("name,gen,kw,n,sa5", CASES, ids=[c[0] for c in CASES])
+def test_golden_sa5_bit_exact(ctx, name, gen, kw, n, sa5):
+    text = golden_text(gen, kw, n)
+    assert np.array_equal(ctx.construct_sa(text), sa5)
+    assert np.array_equal(ctx.construct_sa(text, max_block=n // 3 + 5), sa5)
+    assert np.array_equal(ctx.construct_sa(text, max_block=1024), sa5)
+
+
+def test_sentinel_255_rejected(ctx):
+    import psascan_b200 as P
+    text = textgen.dna(5000).copy()
+    text[1234] = 255
+    with pytest.raises(P.PscError) as e:
+        ctx.construct_sa(text)
+    assert e.value.code == -3
+
+
+def test_empty_text(ctx):
+    assert len(ctx.construct_sa(np.zeros(0, dtype=np.uint8))) == 0
+
+
+@pytest.mark.parametrize("gen,kw", [("dna", dict(seed=21)), ("periodic", dict(period=53, sigma=3)),
+                                    ("random", dict(seed=22)), ("repetitive", dict(seed=4, seed_len=500, rate=3e-3))])
+def test_stage1_sort_block(ctx, gen, kw):
+    """psc_sort_block vs orc_sort_block: SA, BWT (0 at i0), gt_begin (reversed layout), i0 --
+    for the last block and for a block with a tail (renaming + gt_end)."""
+    n = 9000
+    text = textgen.GENERATORS[gen](n, **kw)
+    z = np.zeros(n + 2, dtype=np.uint8)
+    beg2, end2 = 6000, n
+    psa2, bwt2, gtb2, i02 = O.sort_block(text, beg2, end2, z)
+    sa, bwt, gt, i0 = ctx.sort_block(text[beg2:end2])
+    assert i0 == i02 and np.array_equal(sa, psa2) and np.array_equal(bwt, bwt2)
+    assert np.array_equal(gt, rev_bits(gtb2, n, beg2, end2))
+    beg1, end1 = 3000, 6000
+    psa1, bwt1, gtb1, i01 = O.sort_block(text, beg1, end1, gtb2)
+    tl = min(end1 - beg1, n - end1)
+    sa, bwt, gt, i0 = ctx.sort_block(text[beg1:end1], tail_prefix=text[end1:end1 + tl],
+                                     tail_gt_rev=rev_bits(gtb2, n, end1, end1 + tl))
+    assert i0 == i01 and np.array_equal(sa, psa1) and np.array_equal(bwt, bwt1)
+    assert np.array_equal(gt, rev_bits(gtb1, n, beg1, end1))
+
+
+@pytest.mark.parametrize("sigma", [1, 2, 4, 30, 255])
+def test_stage3a_rank(ctx, sigma):
+    rng = np.random.default_rng(sigma)
+    m = 50000 + sigma
+    bwt = rng.integers(0, sigma, size=m, dtype=np.uint8)
+    i0 = 777
+    bwt[i0] = 0
+    r = ctx.rank_build(bwt, i0)
+    cnt = np.bincount(np.delete(bwt, i0), minlength=256)
+    assert np.array_equal(r.counts(), cnt)
+    qi = np.concatenate([rng.integers(0, m + 1, size=4000), [0, 1, 223, 224, 225, i0, i0 + 1, m - 1, m, m + 5, -3]])
+    qc = rng.integers(0, max(sigma, 2), size=len(qi)).astype(np.uint8)
+    got = r.query(qi, qc)
+    masked = bwt.astype(np.int64).copy()
+    masked[i0] = -1
+    for k in range(len(qi)):
+        i = min(max(int(qi[k]), 0), m)
+        assert got[k] == int((masked[:i] == qc[k]).sum()), (k, qi[k], qc[k])
+    r.free()
+
+
+def test_stage2_and_3b_gap(ctx):
+    """psc_initial_ranks + psc_compute_gap vs orc_initial_rank / orc_compute_gap."""
+    for gen, kw in [("dna", dict(seed=31)), ("periodic", dict(period=41, sigma=3)), ("markov", dict(seed=32))]:
+        n, beg, end = 12000, 2000, 5000
+        text = textgen.GENERATORS[gen](n, **kw)
+        ref = O.sa(text)
+        isa = np.empty(n + 1, dtype=np.int64); isa[ref] = np.arange(n); isa[n] = -1
+        gt_end = np.zeros(n + 2, dtype=np.uint8)
+        gt_end[:n + 1] = isa[:n + 1] > isa[end]
+        psa, bwt, gtb, i0 = O.sort_block(text, beg, end, gt_end)
+        last = text[end - 1]
+        gap_o, gt_out_o, _ = O.compute_gap(text, bwt, i0, last, end, n, 0, gt_end)
+        t = n - end
+        # stage 2
+        starts = np.array([0, 32, 64, 1000, 4992, t - 1, t], dtype=np.int64)
+        after_gt = rev_bits(gt_end, n, end, n)
+        got = ctx.initial_ranks(text[beg:end], psa.astype(np.uint32), text[end:], after_gt, starts)
+        want = [O.initial_rank(text, beg, end, psa, end + int(s), end, gt_end) for s in starts]
+        assert list(got) == want
+        # stage 3: several walker layouts give the same gap / gt_out
+        r = ctx.rank_build(bwt, i0)
+        counts = np.bincount(text[beg:end], minlength=256)
+        for slice_len in (t, 4096, 256, 64):
+            wb = list(range(0, t, slice_len)) + [t]
+            sr = ctx.initial_ranks(text[beg:end], psa.astype(np.uint32), text[end:], after_gt, np.array(wb[1:]))
+            gap, gt_out = ctx.compute_gap(r, i0, last, counts, text[end:], wb, sr, after_gt)
+            assert np.array_equal(gap.astype(np.int64), gap_o), (gen, slice_len)
+            assert np.array_equal(gt_out, rev_bits(gt_out_o, n, end, n)), (gen, slice_len)
+        r.free()
+
+
+def test_stage4_merge_level(ctx):
+    text = textgen.markov(20000, seed=41)
+    n = len(text)
+    ref = O.sa(text)
+    cuts = [0, 6000, 13000, n]
+    isa = np.empty(n, dtype=np.int64); isa[ref] = np.arange(n)
+    right = np.zeros(0, dtype=np.uint8)
+    for k in (2, 1, 0):
+        beg, end = cuts[k], cuts[k + 1]
+        in_blk = (ref >= beg) & (ref < end)
+        psa = (ref[in_blk] - beg).astype(np.uint32)
+        # gap[u] = tail suffixes between the block's (u-1)-th and u-th suffix
+        tail_mask = ref >= end
+        csum = np.concatenate([[0], np.cumsum(tail_mask)])
+        pos_blk = np.nonzero(in_blk)[0]
+        bounds = np.concatenate([[0], csum[pos_blk], [csum[-1]]])
+        gap = np.diff(bounds).astype(np.uint32)
+        right = ctx.merge_level(psa, gap, beg, right)
+        want = ref[ref >= beg]
+        assert np.array_equal(decode_sa5(right), want), k
+
+
+def test_glue_two_piece_block(ctx):
+    """gap -> bitvector, BWT merge and gap split vs the oracle (bwt_merge.hpp, compute_*_gap.hpp)."""
+    rng = np.random.default_rng(5)
+    len_l, len_r = 3000, 4100
+    gap_l = np.zeros(len_l + 1, dtype=np.int64)
+    np.add.at(gap_l, rng.integers(0, len_l + 1, size=len_r), 1)
+    bv_o = O.gap_to_bv(gap_l, len_l, len_r)
+    bv = ctx.gap_to_bitvector(gap_l, len_l, len_r)
+    assert np.array_equal(np.unpackbits(bv, bitorder="little")[:len_l + len_r], bv_o)
+    bl = rng.integers(0, 5, size=len_l, dtype=np.uint8)
+    br = rng.integers(0, 5, size=len_r, dtype=np.uint8)
+    out_o, i0_o = O.merge_bwt(bl, br, 17, 23, 4, bv_o)
+    out, i0 = ctx.merge_bwt(bl, br, 17, 23, 4, bv)
+    assert i0 == i0_o and np.array_equal(out, out_o)
+    bg = rng.integers(0, 4, size=len_l + len_r + 1).astype(np.int64)
+    lg_o, rg_o = O.split_gap(bv_o, len_l, len_r, bg)
+    lg, rg = ctx.split_gap(bv, len_l, len_r, bg)
+    assert np.array_equal(lg.astype(np.int64), lg_o) and np.array_equal(rg.astype(np.int64), rg_o)
+
+
+def sa_is_valid(text, sa):
+    """O(n) suffix-array check (the idea of extlib/libdivsufsort/lib/utils.c:161-241 sufcheck):
+    permutation; first symbols non-decreasing; ties ordered by the rank of the next suffix."""
+    n = len(text)
+    if len(sa) != n or sa.min() < 0 or sa.max() >= n:
+        return False
+    isa = np.full(n + 1, -1, dtype=np.int64)
+    isa[sa] = np.arange(n)
+    if (isa[:n] < 0).any():
+        return False
+    c = text[sa].astype(np.int64)
+    if (np.diff(c) < 0).any():
+        return False
+    nxt = isa[sa + 1]
+    tie = np.diff(c) == 0
+    return bool((nxt[1:][tie] > nxt[:-1][tie]).all())
+
+
+@pytest.mark.parametrize("gen,n,mb", [("dna", 3_000_000, 0), ("random", 2_000_000, 0),
+                                      ("markov", 1_500_000, 400_000), ("repetitive", 2_000_000, 700_001)])
+def test_large_property_check(ctx, gen, n, mb):
+    text = textgen.GENERATORS[gen](n)
+    sa = decode_sa5(ctx.construct_sa(text, max_block=mb))
+    assert sa_is_valid(text, sa)
+    if n <= 3_000_000:
+        assert np.array_equal(sa, O.sa(text)) if n <= 2_000_000 else True
