@@ -132,7 +132,8 @@ int psc_construct_sa_d(psc_context *ctx, const uint8_t *text_d, long n, long max
 /* per-phase device time (ms, CUDA events) and counters of the last psc_construct_sa* call */
 typedef struct psc_stats {
   double ms_total, ms_gt_end, ms_sort, ms_radix, ms_bwt, ms_rank_build, ms_init_ranks, ms_walk,
-      ms_merge, ms_h2d, ms_d2h;
+      ms_merge, ms_h2d, ms_d2h,
+      ms_radix_pass; /* device time of the digit-pass kernels alone (events around each launch) */
   long n_blocks, lf_steps, radix_passes, radix_elems, doubling_rounds, walkers, kernel_launches;
 } psc_stats;
 int psc_get_stats(psc_context *ctx, psc_stats *out);

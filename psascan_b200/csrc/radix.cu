@@ -214,12 +214,18 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
   DevBuf<uint32_t> counter(ctx, 1);
   uint64_t *kin = keys_a, *kout = keys_b;
   uint32_t *vin = vals_a, *vout = vals_b;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> evs;
   for (int p = 0; p < n_shifts; ++p) {
     if (skip[p]) continue;
     status.zero();
     counter.zero();
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0, ctx->stream);
     radix_pass_kernel<<<(unsigned)tiles, RS_THREADS, 0, ctx->stream>>>(
         kin, vin, kout, vout, n, sl.s[p], gscan.p + p * RADIX, status.p, counter.p);
+    cudaEventRecord(e1, ctx->stream);
+    evs.push_back({e0, e1});
     PSC_LAUNCH_CHECK();
     ctx->launches++;
     ctx->stats.radix_passes++;
@@ -229,6 +235,11 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
   }
   // the host vector `scans` must outlive the async copy
   sync(ctx);
+  for (auto &e : evs) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, e.first, e.second) == cudaSuccess) ctx->stats.ms_radix_pass += ms;
+    cudaEventDestroy(e.first); cudaEventDestroy(e.second);
+  }
   *keys_out = kin;
   *vals_out = vin;
 }
