@@ -67,12 +67,12 @@ int psc_bench_radix_pass(psc_context *ctx, long n, int iters, double *ms_per_pas
     int shifts[1] = {0};
     uint64_t *ko; uint32_t *vo;
     radix_sort_pairs(ctx, ka.p, va.p, kb.p, vb.p, n, shifts, 1, &ko, &vo);  // warm-up
-    double before = ctx->stats.ms_radix;
+    double before = ctx->stats.ms_radix_pass;
     for (int k = 0; k < iters; ++k) {
       shifts[0] = 8 * (k % 8);
       radix_sort_pairs(ctx, ka.p, va.p, kb.p, vb.p, n, shifts, 1, &ko, &vo);
     }
-    *ms_per_pass = (ctx->stats.ms_radix - before) / iters;
+    *ms_per_pass = (ctx->stats.ms_radix_pass - before) / iters;
     return PSC_OK;
   } catch (const CudaError &e) { return e.code; }
 }

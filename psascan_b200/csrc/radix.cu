@@ -14,10 +14,6 @@
 namespace psc {
 
 constexpr int RADIX = 256;
-constexpr int RS_THREADS = 256;
-constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_ITEMS = 16;
-constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 4096 pairs = 48 KB of input per tile
 constexpr int MAX_PASSES = 8;
 
 struct ShiftList { int s[MAX_PASSES]; int n; };
@@ -55,122 +51,183 @@ __global__ void __launch_bounds__(512) radix_hist_kernel(const uint64_t *__restr
 }
 
 // ---- one digit pass -----------------------------------------------------------------------
-__global__ void __launch_bounds__(RS_THREADS)
+// Shared memory (dynamic): stage[TILE] u64 (keys, then reused for the values) | gbase_adj[256] u32 (+pad) |
+// warp_hist[WARPS][256] u32 | digit_off[256] u32 | wsum[8] u32 + tile id
+template <int THREADS, int ITEMS>
+struct PassCfg {
+  static constexpr int WARPS = THREADS / 32;
+  static constexpr int TILE = THREADS * ITEMS;
+  static constexpr size_t SMEM = (size_t)WARPS * RADIX * 4 + RADIX * 4 + RADIX * 8 + 64 + (size_t)TILE * 8;  // gbase: 2*RADIX u32
+};
+
+// lanes of the warp holding the same digit.  USE_MATCH: match.any (one ADU instruction, measured
+// ~60 cycles of the SM's ADU pipe per warp) else eight ballots (ALU/vote pipes).  The pass kernel
+// mixes both per item so neither pipe saturates.
+template <bool USE_MATCH>
+__device__ __forceinline__ uint32_t digit_peers(int d) {
+  if (USE_MATCH) return __match_any_sync(0xffffffffu, d);
+  uint32_t peers = 0xffffffffu;
+#pragma unroll
+  for (int b = 0; b < 8; ++b) {
+    bool bit = (d >> b) & 1;
+    uint32_t bal = __ballot_sync(0xffffffffu, bit);
+    peers &= bal ^ (bit ? 0u : 0xffffffffu);
+  }
+  return peers;
+}
+
+template <int THREADS, int ITEMS, int MINB, int MATCH>
+__global__ void __launch_bounds__(THREADS, MINB)
     radix_pass_kernel(const uint64_t *__restrict__ kin, const uint32_t *__restrict__ vin,
                       uint64_t *__restrict__ kout, uint32_t *__restrict__ vout, long n, int shift,
                       const uint64_t *__restrict__ gscan,  // [256] exclusive global digit offsets
                       uint64_t *status,                    // [tiles][256] look-back chain
                       uint32_t *tile_counter) {
-  __shared__ uint32_t warp_hist[RS_WARPS][RADIX];
-  __shared__ uint32_t digit_off[RADIX];
-  __shared__ long long gbase_adj[RADIX];
-  __shared__ uint32_t wsum[RS_WARPS];
-  __shared__ uint32_t s_tile;
-  __shared__ __align__(16) uint64_t stage[RS_TILE];
+  constexpr int WARPS = THREADS / 32;
+  constexpr int TILE = THREADS * ITEMS;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  uint64_t *stage = reinterpret_cast<uint64_t *>(smem_raw);
+  uint32_t *gbase_adj = reinterpret_cast<uint32_t *>(stage + TILE);  // [RADIX] (+RADIX pad)
+  uint32_t *warp_hist = gbase_adj + 2 * RADIX;  // [WARPS][RADIX]
+  uint32_t *digit_off = warp_hist + WARPS * RADIX;
+  uint32_t *wsum = digit_off + RADIX;  // [8] + s_tile at [8]
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
-  for (int i = tid; i < RS_WARPS * RADIX; i += RS_THREADS) (&warp_hist[0][0])[i] = 0;
+  if (tid == 0) wsum[8] = atomicAdd(tile_counter, 1u);
+  for (int i = tid; i < WARPS * RADIX; i += THREADS) warp_hist[i] = 0;
   __syncthreads();
-  const long tile = s_tile;
-  const long tile_beg = tile * RS_TILE;
-  const int valid = (int)min((long)RS_TILE, n - tile_beg);
+  const long tile = wsum[8];
+  const long tile_beg = tile * TILE;
+  const int valid = (int)min((long)TILE, n - tile_beg);
 
   // load: element order inside the tile is (warp, item, lane)
-  uint64_t key[RS_ITEMS];
-  uint32_t val[RS_ITEMS];
-  uint16_t rnk[RS_ITEMS];
-  const int wbase = warp * (RS_ITEMS * 32) + lane;
+  uint64_t key[ITEMS];
+  uint32_t val[ITEMS];
+  uint16_t rnk[ITEMS];
+  const int wbase = warp * (ITEMS * 32) + lane;
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; ++k) {
+  for (int k = 0; k < ITEMS; ++k) {
     int e = wbase + k * 32;
     if (e < valid) { key[k] = kin[tile_beg + e]; val[k] = vin[tile_beg + e]; }
     else { key[k] = ~0ull; val[k] = 0; }
   }
-  // rank inside the warp
-  const uint32_t lane_lt = (1u << lane) - 1;
-  uint32_t *wh = warp_hist[warp];
+  // early counts: per-warp digit histogram (fire-and-forget shared atomics, no dependent chain)
+  uint32_t *wh = warp_hist + warp * RADIX;
+  int dgt[ITEMS];
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; ++k) {
-    int d = (int)((key[k] >> shift) & 255);
-    uint32_t peers = __match_any_sync(0xffffffffu, d);
-    int leader = 31 - __clz(peers);
-    uint32_t base = 0;
-    if (lane == leader) { base = wh[d]; wh[d] = base + __popc(peers); }
-    base = __shfl_sync(0xffffffffu, base, leader);
-    rnk[k] = (uint16_t)(base + __popc(peers & lane_lt));
-    __syncwarp();
+  for (int k = 0; k < ITEMS; ++k) { dgt[k] = (int)((key[k] >> shift) & 255); atomicAdd(&wh[dgt[k]], 1u); }
+  __syncthreads();
+  // per digit (thread = digit): tile count, exclusive scan over digits, per-warp start offsets
+  uint32_t cnt = 0, incl = 0;
+  if (tid < RADIX) {
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) cnt += warp_hist[w * RADIX + tid];
+    incl = cnt;  // padding keys included: they sit at the tile's end
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) wsum[warp] = incl;
   }
   __syncthreads();
-  // per digit (thread = digit): prefix over warps, tile count
-  uint32_t cnt = 0;
-  {
+  if (tid < RADIX) {
+    uint32_t woff = 0;
 #pragma unroll
-    for (int w = 0; w < RS_WARPS; ++w) { uint32_t t = warp_hist[w][tid]; warp_hist[w][tid] = cnt; cnt += t; }
-  }
-  // exclusive scan of the 256 tile counts (padding keys included: they sit at the tile's end)
-  uint32_t incl = cnt;
+    for (int w = 0; w < 8; ++w) if (w < warp) woff += wsum[w];
+    const uint32_t doff = woff + incl - cnt;
+    digit_off[tid] = doff;
+    uint32_t run = doff;
 #pragma unroll
-  for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
-  if (lane == 31) wsum[warp] = incl;
-  __syncthreads();
-  uint32_t woff = 0;
-#pragma unroll
-  for (int w = 0; w < RS_WARPS; ++w) if (w < warp) woff += wsum[w];
-  const uint32_t doff = woff + incl - cnt;
-  digit_off[tid] = doff;
-  // publish + look back
-  uint32_t cnt_valid = cnt;
-  if (tid == 255) cnt_valid -= (uint32_t)(RS_TILE - valid);
-  uint64_t excl = 0;
-  uint64_t *my = status + (size_t)tile * RADIX + tid;
-  if (tile == 0) {
-    st_relaxed_u64(my, ST_INCL | cnt_valid);
-  } else {
-    st_relaxed_u64(my, ST_LOCAL | cnt_valid);
-    long t = tile - 1;
-    while (true) {
-      uint64_t v = ld_relaxed_u64(status + (size_t)t * RADIX + tid);
-      uint64_t f = v & ~ST_MASK;
-      if (f == 0) continue;
-      excl += v & ST_MASK;
-      if (f == ST_INCL) break;
-      --t;
+    for (int w = 0; w < WARPS; ++w) { uint32_t t = warp_hist[w * RADIX + tid]; warp_hist[w * RADIX + tid] = run; run += t; }
+    // publish + look back
+    uint32_t cnt_valid = cnt;
+    if (tid == 255) cnt_valid -= (uint32_t)(TILE - valid);
+    uint64_t excl = 0;
+    uint64_t *my = status + (size_t)tile * RADIX + tid;
+    if (tile == 0) {
+      st_relaxed_u64(my, ST_INCL | cnt_valid);
+    } else {
+      st_relaxed_u64(my, ST_LOCAL | cnt_valid);
+      long t = tile - 1;
+      while (true) {
+        uint64_t v = ld_relaxed_u64(status + (size_t)t * RADIX + tid);
+        uint64_t f = v & ~ST_MASK;
+        if (f == 0) continue;
+        excl += v & ST_MASK;
+        if (f == ST_INCL) break;
+        --t;
+      }
+      st_relaxed_u64(my, ST_INCL | (excl + cnt_valid));
     }
-    st_relaxed_u64(my, ST_INCL | (excl + cnt_valid));
+    gbase_adj[tid] = (uint32_t)(gscan[tid] + excl) - doff;  // n < 2^32: index arithmetic mod 2^32
   }
-  gbase_adj[tid] = (long long)(gscan[tid] + excl) - (long long)doff;
   __syncthreads();
-  // keys -> shared memory in digit order
+  // ranks: peers of each item, then one shared atomic per distinct digit (issued back to back;
+  // same-address atomics of one warp retire in issue order, which keeps the sort stable)
+  const uint32_t lane_lt = (1u << lane) - 1;
+  uint32_t peers[ITEMS];
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; ++k) {
-    int d = (int)((key[k] >> shift) & 255);
-    uint32_t pos = digit_off[d] + wh[d] + rnk[k];
+  for (int k = 0; k < ITEMS; ++k)
+    peers[k] = (k < MATCH) ? digit_peers<true>(dgt[k]) : digit_peers<false>(dgt[k]);
+  uint32_t base[ITEMS];
+  int lead[ITEMS];
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    lead[k] = 31 - __clz(peers[k]);
+    base[k] = 0;
+    if (lane == lead[k]) base[k] = atomicAdd(&wh[dgt[k]], (uint32_t)__popc(peers[k]));
+  }
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    uint32_t pos = __shfl_sync(0xffffffffu, base[k], lead[k]) + __popc(peers[k] & lane_lt);
     rnk[k] = (uint16_t)pos;
     stage[pos] = key[k];
   }
   __syncthreads();
-  uint8_t dg[RS_ITEMS];
+  uint8_t dg[ITEMS];
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; ++k) {
-    int i = tid + k * RS_THREADS;
+  for (int k = 0; k < ITEMS; ++k) {
+    int i = tid + k * THREADS;
     if (i < valid) {
       uint64_t kk = stage[i];
       int d = (int)((kk >> shift) & 255);
       dg[k] = (uint8_t)d;
-      kout[gbase_adj[d] + i] = kk;
+      kout[(uint32_t)(gbase_adj[d] + (uint32_t)i)] = kk;
     }
   }
   __syncthreads();
   uint32_t *vstage = reinterpret_cast<uint32_t *>(stage);
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; ++k) vstage[rnk[k]] = val[k];
+  for (int k = 0; k < ITEMS; ++k) vstage[rnk[k]] = val[k];
   __syncthreads();
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; ++k) {
-    int i = tid + k * RS_THREADS;
-    if (i < valid) vout[gbase_adj[dg[k]] + i] = vstage[i];
+  for (int k = 0; k < ITEMS; ++k) {
+    int i = tid + k * THREADS;
+    if (i < valid) vout[(uint32_t)(gbase_adj[dg[k]] + (uint32_t)i)] = vstage[i];
   }
+}
+
+typedef void (*PassFn)(const uint64_t *, const uint32_t *, uint64_t *, uint32_t *, long, int, const uint64_t *,
+                       uint64_t *, uint32_t *);
+struct PassVariant { const char *name; PassFn fn; int threads, tile; size_t smem; };
+#define PASS_VARIANT(T, I, B, M) \
+  { #T "x" #I "b" #B "m" #M, radix_pass_kernel<T, I, B, M>, T, PassCfg<T, I>::TILE, PassCfg<T, I>::SMEM }
+// first entry = default (measured best on B200: 2.17 ms per pass of 2^28 pairs = 2.97 TB/s);
+// PSC_RADIX_VARIANT selects another one for tuning runs (tools/tune_radix.py)
+static const PassVariant g_variants[] = {
+    PASS_VARIANT(512, 12, 2, 0), PASS_VARIANT(384, 12, 3, 0), PASS_VARIANT(512, 8, 3, 0), PASS_VARIANT(512, 16, 2, 0),
+    PASS_VARIANT(256, 12, 4, 0), PASS_VARIANT(1024, 8, 1, 0), PASS_VARIANT(512, 12, 2, 12),
+};
+static const PassVariant &pass_variant() {
+  static int idx = -1;
+  if (idx < 0) {
+    idx = 0;
+    if (const char *e = getenv("PSC_RADIX_VARIANT")) {
+      for (size_t i = 0; i < sizeof(g_variants) / sizeof(g_variants[0]); ++i)
+        if (!strcmp(e, g_variants[i].name)) idx = (int)i;
+    }
+    for (auto &v : g_variants)
+      cudaFuncSetAttribute((const void *)v.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v.smem);
+  }
+  return g_variants[idx];
 }
 
 void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint64_t *keys_b,
@@ -209,7 +266,8 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
   DevBuf<uint64_t> gscan(ctx, MAX_PASSES * RADIX);
   h2d(ctx, gscan.p, scans.data(), scans.size());
 
-  long tiles = div_up(n, RS_TILE);
+  const PassVariant &pv = pass_variant();
+  long tiles = div_up(n, pv.tile);
   DevBuf<uint64_t> status(ctx, (size_t)tiles * RADIX);
   DevBuf<uint32_t> counter(ctx, 1);
   uint64_t *kin = keys_a, *kout = keys_b;
@@ -222,7 +280,7 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     cudaEventRecord(e0, ctx->stream);
-    radix_pass_kernel<<<(unsigned)tiles, RS_THREADS, 0, ctx->stream>>>(
+    pv.fn<<<(unsigned)tiles, pv.threads, pv.smem, ctx->stream>>>(
         kin, vin, kout, vout, n, sl.s[p], gscan.p + p * RADIX, status.p, counter.p);
     cudaEventRecord(e1, ctx->stream);
     evs.push_back({e0, e1});
