@@ -118,7 +118,7 @@ static void construct_sa_device(psc_context *ctx, const uint8_t *text_d, long n,
       sort_block(ctx, block_d, m, t > 0 ? gt_end.p : nullptr, &res);
       if (id > 0) {
         PSC_CUDA(cudaMemsetAsync(gt_new, 0, gwords * 4, ctx->stream));
-        gt_begin_from_isa(ctx, res.isa.p, m, (uint32_t)res.i0, gt_new, beg);
+        gt_begin_from_sa(ctx, res.sa.p, m, (uint32_t)res.i0, gt_new, beg);
         or_not_bit_kernel<<<1, 1, 0, ctx->stream>>>(t > 0 ? gt_end.p : nullptr, 0, 1, gt_new, end - 1);
         PSC_LAUNCH_CHECK();
         ctx->launches++;

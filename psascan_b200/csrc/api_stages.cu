@@ -70,7 +70,7 @@ int psc_sort_block(psc_context *ctx, const uint8_t *text, long m, const uint8_t 
     if (gt_begin_rev) {
       DevBuf<uint32_t> g(ctx, m / 32 + 2);
       g.zero();
-      gt_begin_from_isa(ctx, res.isa.p, m, (uint32_t)res.i0, g.p, 0);
+      gt_begin_from_sa(ctx, res.sa.p, m, (uint32_t)res.i0, g.p, 0);
       or_not_bit2_kernel<<<1, 1, 0, ctx->stream>>>(t ? gt_end.p : nullptr, 1, g.p, m - 1);
       PSC_LAUNCH_CHECK();
       download_gt(ctx, g.p, m, gt_begin_rev);

@@ -160,7 +160,7 @@ void exclusive_scan_u32_to_u64(psc_context *ctx, const uint32_t *in, uint64_t *o
 // sufsort.cu
 struct BlockSortResult {
   DevBuf<uint32_t> sa;    // m
-  DevBuf<uint32_t> isa;   // m
+  DevBuf<uint32_t> isa;   // m, only allocated when doubling rounds were needed
   long i0 = 0;
 };
 // text_d: the block (m symbols, followed in memory by the tail when after_len > 0 is served
@@ -175,12 +175,12 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
 void compute_gt_end(psc_context *ctx, const uint8_t *block_d, long m, const uint8_t *after_d,
                     long after_len, int after_is_text_end, const uint32_t *gt_after_bits_d,
                     long gt_after_off, uint32_t *gt_end_bits_d);
-// K3: BWT (0 at i0) and forward gt_begin bits: bit p-1 (p in [1,m)) <-> isa[p] > i0.
+// K3: BWT (0 at i0) and forward gt_begin bits: bit p-1 (p in [1,m)) <-> rank(p) > i0.
 void bwt_from_sa(psc_context *ctx, const uint8_t *text_d, const uint32_t *sa_d, long m,
                  uint8_t *bwt_d);
-void gt_begin_from_isa(psc_context *ctx, const uint32_t *isa_d, long m, uint32_t i0,
-                       uint32_t *bits_d, long bit_off /* bit bit_off+q <-> position q+1, q in [0,m-1);
-                       the array must be zero there */);
+void gt_begin_from_sa(psc_context *ctx, const uint32_t *sa_d, long m, uint32_t i0,
+                      uint32_t *bits_d, long bit_off /* bit bit_off+q <-> position q+1, q in [0,m-1);
+                      the array must be zero there */);
 
 // bit-vector layout conversion: forward bits (bit q <-> position lo+q+1) <-> reversed LSB-first
 // bytes with hi = lo + nbits (bit r <-> position hi - r).

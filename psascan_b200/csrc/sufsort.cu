@@ -106,16 +106,17 @@ __global__ void __launch_bounds__(SC_THREADS)
   if (threadIdx.x == 0) { agg_act[blockIdx.x] = tot_act; agg_head[blockIdx.x] = tot_head; }
 }
 
-// Applies one round: writes SA and ISA for the sorted elements and compacts the still-active
-// ones into (keyY = new group head << 32, valY = text position, posY = SA slot).
-//   pos == nullptr: element j sits in SA slot j (round 0).
+// Applies one round: writes SA (and ISA when it exists) for the sorted elements and compacts the
+// still-active ones into (keyY = new group head, valY = text position, posY = SA slot).
+//   pos == nullptr: element j sits in SA slot j (round 0); sa == nullptr: the sorted value
+//   array itself is the SA (round 0), only active elements are touched.
 __global__ void __launch_bounds__(SC_THREADS)
     group_apply_kernel(const uint64_t *__restrict__ K, const uint32_t *__restrict__ V,
                        const uint32_t *__restrict__ pos, long n,
                        const uint64_t *__restrict__ agg_act, const uint64_t *__restrict__ agg_head,
                        uint32_t *__restrict__ sa, uint32_t *__restrict__ isa,
                        uint64_t *__restrict__ keyY, uint32_t *__restrict__ valY,
-                       uint32_t *__restrict__ posY) {
+                       uint32_t *__restrict__ posY, uint32_t *__restrict__ i0_out) {
   __shared__ uint64_t sm[SC_THREADS / 32 + 1];
   const long base = (long)blockIdx.x * PD_TILE + (long)threadIdx.x * PD_ITEMS;
   bool head[PD_ITEMS], act[PD_ITEMS];
@@ -149,12 +150,14 @@ __global__ void __launch_bounds__(SC_THREADS)
     if (i >= n) break;
     if (head[k]) { hd = (uint64_t)i + 1; hp_valid = false; }
     if (!hp_valid) { hp = pos ? pos[hd - 1] : (uint32_t)(hd - 1); hp_valid = true; }
+    if (!act[k] && sa == nullptr) continue;  // round 0: singletons stay where the sort put them
     uint32_t v = V[i];
     uint32_t slot = pos ? pos[i] : (uint32_t)i;
-    sa[slot] = v;
-    isa[v] = hp;
+    if (sa) sa[slot] = v;
+    if (isa) isa[v] = hp;
+    if (v == 0 && i0_out) *i0_out = slot;
     if (act[k]) {
-      keyY[act_off] = (uint64_t)hp << 32;
+      keyY[act_off] = (uint64_t)hp;
       valY[act_off] = v;
       posY[act_off] = slot;
       ++act_off;
@@ -162,7 +165,7 @@ __global__ void __launch_bounds__(SC_THREADS)
   }
 }
 
-// second half of the next key: ISA[position + h] + 1, 0 when past the block end
+// next key from the ISA: (group head << 32) | ISA[position + h] + 1, 0 when past the block end
 __global__ void __launch_bounds__(256)
     second_key_kernel(uint64_t *__restrict__ keyY, const uint32_t *__restrict__ valY, long a,
                       const uint32_t *__restrict__ isa, long m, long h) {
@@ -170,7 +173,67 @@ __global__ void __launch_bounds__(256)
   if (j >= a) return;
   long p = (long)valY[j] + h;
   uint32_t r = p < m ? isa[p] + 1u : 0u;
-  keyY[j] |= (uint64_t)r;
+  keyY[j] = (keyY[j] << 32) | (uint64_t)r;
+}
+
+__device__ __forceinline__ uint32_t renamed_code(const uint8_t *__restrict__ text, long m,
+                                                 const uint32_t *__restrict__ gt_end, const RenameLut &lut,
+                                                 long i) {
+  if (i >= m) return 0;
+  int c = text[i];
+  if (c == lut.last && (i == m - 1 || gt_end == nullptr || bit_get(gt_end, i + 1))) return lut.code_last_high;
+  return lut.code[c];
+}
+
+// next key straight from the text ("text round"): (group head << k1*bits) | the k1 renamed symbols
+// that follow the h already compared.  Needs no ISA, so texts whose ties die out within
+// h + k1 symbols never pay for the m-element ISA scatter.
+__global__ void __launch_bounds__(256)
+    second_key_text_kernel(uint64_t *__restrict__ keyY, const uint32_t *__restrict__ valY, long a,
+                           const uint8_t *__restrict__ text, long m, const uint32_t *__restrict__ gt_end,
+                           RenameLut lut, long h, int k1) {
+  long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= a) return;
+  long p = (long)valY[j] + h;
+  uint64_t key = keyY[j];
+  for (int s = 0; s < k1; ++s) key = (key << lut.bits) | renamed_code(text, m, gt_end, lut, p + s);
+  keyY[j] = key;
+}
+
+// isa[sa[i]] = i for the whole block (only when doubling rounds are needed), then the group heads
+// of the active elements on top
+__global__ void __launch_bounds__(256)
+    isa_scatter_kernel(const uint32_t *__restrict__ sa, long m, uint32_t *__restrict__ isa) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < m) isa[sa[i]] = (uint32_t)i;
+}
+__global__ void __launch_bounds__(256)
+    isa_fix_kernel(const uint64_t *__restrict__ keyY, const uint32_t *__restrict__ valY, long a,
+                   uint32_t *__restrict__ isa) {
+  long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < a) isa[valY[j]] = (uint32_t)keyY[j];
+}
+
+// position of text position 0 in the round-0 order: only the group of key0(0) is searched
+__global__ void __launch_bounds__(256)
+    find_i0_kernel(const uint64_t *__restrict__ K, const uint32_t *__restrict__ V, long m,
+                   const uint64_t *__restrict__ key_of_zero, uint32_t *__restrict__ i0_out) {
+  __shared__ long s_lo, s_hi;
+  if (threadIdx.x == 0) {
+    uint64_t k0 = *key_of_zero;
+    long lo = 0, hi = m;
+    while (lo < hi) { long mid = (lo + hi) >> 1; if (K[mid] < k0) lo = mid + 1; else hi = mid; }
+    s_lo = lo;
+    hi = m;
+    while (lo < hi) { long mid = (lo + hi) >> 1; if (K[mid] <= k0) lo = mid + 1; else hi = mid; }
+    s_hi = lo;
+  }
+  __syncthreads();
+  long beg = (long)blockIdx.x * 4096, end = min(beg + 4096, m);
+  beg = max(beg, s_lo);
+  end = min(end, s_hi);
+  for (long i = beg + threadIdx.x; i < end; i += blockDim.x)
+    if (V[i] == 0) *i0_out = (uint32_t)i;
 }
 
 static int bits_for(uint64_t v) { int b = 0; while (v) { ++b; v >>= 1; } return b; }
@@ -179,9 +242,8 @@ static int bits_for(uint64_t v) { int b = 0; while (v) { ++b; v >>= 1; } return 
 void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t *gt_end_bits_d,
                 BlockSortResult *res) {
   PhaseTimer timer(ctx, &ctx->stats.ms_sort);
-  res->sa.alloc(ctx, m);
-  res->isa.alloc(ctx, m);
-  if (m == 0) return;
+  res->isa.release();
+  if (m == 0) { res->sa.alloc(ctx, 0); return; }
   uint8_t last = 0;
   PSC_CUDA(cudaMemcpyAsync(&last, text_d + m - 1, 1, cudaMemcpyDeviceToHost, ctx->stream));
   sync(ctx);
@@ -235,18 +297,32 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
       text_d, m, gt_end_bits_d, lut, keyA.p, valA.p);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
+  DevBuf<uint64_t> key_of_zero(ctx, 1), total_d(ctx, 1);
+  DevBuf<uint32_t> i0_d(ctx, 1);
+  PSC_CUDA(cudaMemcpyAsync(key_of_zero.p, keyA.p, 8, cudaMemcpyDeviceToDevice, ctx->stream));
 
   int shifts[8];
   for (int p = 0; p < passes; ++p) shifts[p] = 8 * p;
   uint64_t *K; uint32_t *V;
   radix_sort_pairs(ctx, keyA.p, valA.p, keyB.p, valB.p, m, shifts, passes, &K, &V);
+  find_i0_kernel<<<(unsigned)div_up(m, 4096), 256, 0, ctx->stream>>>(K, V, m, key_of_zero.p, i0_d.p);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
 
-  DevBuf<uint32_t> posA, posB;
+  // the sorted position array IS the suffix array from here on; later rounds patch the slots of
+  // suffixes that were still tied.  The other value buffer and both key buffers become scratch.
+  const bool v_is_a = (V == valA.p);
+  res->sa = std::move(v_is_a ? valA : valB);
+  DevBuf<uint32_t> &vfree = v_is_a ? valB : valA;
+  uint64_t *kbuf[2] = {(K == keyA.p) ? keyB.p : keyA.p, K};  // compaction goes to kbuf[0] first
+  DevBuf<uint32_t> valC;                                     // second value buffer, sized once `a` is known
+  uint32_t *vbuf[2] = {vfree.p, nullptr};
+  DevBuf<uint32_t> posbuf[2];
   uint32_t *pos = nullptr;  // round 0: identity
-  long a = m;
-  long h = k;
-  DevBuf<uint64_t> total_d(ctx, 1);
-  const int lowb = bits_for((uint64_t)m), highb = bits_for((uint64_t)(m > 1 ? m - 1 : 1));
+  int out = 0, pout = 0;    // which (kbuf, vbuf) pair / posbuf the next compaction writes
+  long a = m, h = k;
+  const int hpbits = bits_for((uint64_t)(m > 1 ? m - 1 : 1)), lowb = bits_for((uint64_t)m);
+  bool text_round_done = false;
   for (int round = 0;; ++round) {
     long t = div_up(a, PD_TILE);
     DevBuf<uint64_t> agg_act(ctx, t), agg_head(ctx, t);
@@ -257,32 +333,56 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
     uint64_t na = 0;
     d2h(ctx, &na, total_d.p, 1);
     sync(ctx);
-    // outputs of the compaction go to the buffer pair the sort result is NOT in
-    uint64_t *KY = (K == keyA.p) ? keyB.p : keyA.p;
-    uint32_t *VY = (V == valA.p) ? valB.p : valA.p;
-    DevBuf<uint32_t> &posY = (pos == posA.p && pos != nullptr) ? posB : posA;
-    posY.alloc(ctx, na);
+    if (round == 0 && na > 0) {
+      valC.alloc(ctx, na);
+      vbuf[1] = valC.p;
+    }
+    posbuf[pout].alloc(ctx, na);
     group_apply_kernel<<<(unsigned)t, SC_THREADS, 0, ctx->stream>>>(
-        K, V, pos, a, agg_act.p, agg_head.p, res->sa.p, res->isa.p, KY, VY, posY.p);
+        K, V, pos, a, agg_act.p, agg_head.p, round == 0 ? nullptr : res->sa.p, res->isa.p, kbuf[out], vbuf[out],
+        posbuf[pout].p, i0_d.p);
     PSC_LAUNCH_CHECK();
     ctx->launches += 2;
     ctx->stats.doubling_rounds++;
     if (na == 0) break;
     a = (long)na;
-    second_key_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, res->isa.p, m, h);
-    PSC_LAUNCH_CHECK();
-    ctx->launches++;
-    pos = posY.p;
+    uint64_t *KY = kbuf[out];
+    uint32_t *VY = vbuf[out];
+    pos = posbuf[pout].p;
+    pout ^= 1;
     int nsh = 0;
-    for (int b = 0; b < lowb; b += 8) shifts[nsh++] = b;
-    for (int b = 0; b < highb; b += 8) shifts[nsh++] = 32 + b;
-    uint64_t *KO = (KY == keyA.p) ? keyB.p : keyA.p;
-    uint32_t *VO = (VY == valA.p) ? valB.p : valA.p;
-    radix_sort_pairs(ctx, KY, VY, KO, VO, a, shifts, nsh, &K, &V);
-    h *= 2;
+    const int k1 = (64 - hpbits) / lut.bits;
+    if (!text_round_done && k1 >= 1) {
+      // text round: extend the compared prefix by k1 symbols read from the text (no ISA yet)
+      text_round_done = true;
+      second_key_text_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, text_d, m, gt_end_bits_d,
+                                                                                lut, h, k1);
+      PSC_LAUNCH_CHECK();
+      for (int b = 0; b < k1 * lut.bits + hpbits; b += 8) shifts[nsh++] = b;
+      h += k1;
+    } else {
+      text_round_done = true;
+      if (res->isa.p == nullptr) {
+        // first doubling round: now the full inverse suffix array is needed
+        res->isa.alloc(ctx, m);
+        isa_scatter_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(res->sa.p, m, res->isa.p);
+        PSC_LAUNCH_CHECK();
+        isa_fix_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, res->isa.p);
+        PSC_LAUNCH_CHECK();
+        ctx->launches += 2;
+      }
+      second_key_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, res->isa.p, m, h);
+      PSC_LAUNCH_CHECK();
+      for (int b = 0; b < lowb; b += 8) shifts[nsh++] = b;
+      for (int b = 0; b < hpbits; b += 8) shifts[nsh++] = 32 + b;
+      h *= 2;
+    }
+    ctx->launches++;
+    radix_sort_pairs(ctx, KY, VY, kbuf[1 - out], vbuf[1 - out], a, shifts, nsh, &K, &V);
+    out = (K == kbuf[0]) ? 1 : 0;  // next compaction must not overwrite the sorted arrays
   }
   uint32_t i0 = 0;
-  d2h(ctx, &i0, res->isa.p, 1);
+  d2h(ctx, &i0, i0_d.p, 1);
   sync(ctx);
   res->i0 = i0;
 }
@@ -338,24 +438,25 @@ void bwt_from_sa(psc_context *ctx, const uint8_t *text_d, const uint32_t *sa_d, 
   ctx->launches++;
 }
 
-// bit bit_off+q <-> block position q+1 (q+1 < m): isa[q+1] > i0.
+// bit bit_off+q <-> block position q+1: rank(q+1) > i0.  Scatter of single bits from the SA side
+// (the bit array of a block is at most a few hundred MB and mostly L2-resident).
 __global__ void __launch_bounds__(256)
-    gt_begin_kernel(const uint32_t *__restrict__ isa, long m, uint32_t i0, uint32_t *__restrict__ bits,
+    gt_begin_kernel(const uint32_t *__restrict__ sa, long m, uint32_t i0, uint32_t *__restrict__ bits,
                     long bit_off) {
-  long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  bool g = (q + 1 < m) && (isa[q + 1] > i0);
-  uint32_t word = __ballot_sync(0xffffffffu, g);
-  if ((threadIdx.x & 31) == 0) {
-    long rem = (m - 1) - q;
-    store_bits_word(bits, bit_off + q, word, rem >= 32 ? 32 : (int)rem);
-  }
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x + (long)i0 + 1;
+  if (i >= m) return;
+  uint32_t p = sa[i];
+  if (p == 0) return;
+  long b = bit_off + (long)p - 1;
+  atomicOr(&bits[b >> 5], 1u << (b & 31));
 }
 
-void gt_begin_from_isa(psc_context *ctx, const uint32_t *isa_d, long m, uint32_t i0,
-                       uint32_t *bits_d, long bit_off) {
+void gt_begin_from_sa(psc_context *ctx, const uint32_t *sa_d, long m, uint32_t i0, uint32_t *bits_d,
+                      long bit_off) {
   PhaseTimer timer(ctx, &ctx->stats.ms_bwt);
-  if (m <= 1) return;
-  gt_begin_kernel<<<(unsigned)div_up(m - 1, 256), 256, 0, ctx->stream>>>(isa_d, m, i0, bits_d, bit_off);
+  long cnt = m - 1 - (long)i0;
+  if (cnt <= 0) return;
+  gt_begin_kernel<<<(unsigned)div_up(cnt, 256), 256, 0, ctx->stream>>>(sa_d, m, i0, bits_d, bit_off);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
 }
