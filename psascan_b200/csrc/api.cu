@@ -99,8 +99,6 @@ static void construct_sa_device(psc_context *ctx, const uint8_t *text_d, long n,
     Ga.alloc(ctx, gwords); Gb.alloc(ctx, gwords);
     Ga.zero(); Gb.zero();
     for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); Mhi[k].alloc(ctx, n); }
-  } else {
-    Mlo[0].alloc(ctx, n); Mhi[0].alloc(ctx, n);
   }
   uint32_t *gt_cur = Ga.p, *gt_new = Gb.p;
   int cur = 0;
@@ -132,7 +130,13 @@ static void construct_sa_device(psc_context *ctx, const uint8_t *text_d, long n,
       gap_of_block(ctx, block_d, m, res.sa.p, res.i0, after_d, t, gt_cur, end, id > 0 ? gt_new : nullptr,
                    gap.p);
     }
-    int nxt = B > 1 ? 1 - cur : 0;
+    if (B == 1) {  // one piece: the block SA goes straight to the 40-bit writer
+      pack_sa5_from_sa(ctx, res.sa.p, n, 0, out_sa5_d);
+      sync(ctx);
+      ctx->stats.kernel_launches = ctx->launches;
+      return;
+    }
+    int nxt = 1 - cur;
     merge_level(ctx, res.sa.p, gap.p, m, beg, Mlo[cur].p, Mhi[cur].p, right_len, Mlo[nxt].p, Mhi[nxt].p);
     cur = nxt;
     right_len += m;

@@ -151,7 +151,9 @@ __device__ __forceinline__ long common_prefix(const uint8_t *a, const uint8_t *b
 // (one of the two buffer pairs).  Passes whose digit is constant over all keys are skipped.
 void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint64_t *keys_b,
                       uint32_t *vals_b, long n, const int *shifts, int n_shifts,
-                      uint64_t **keys_out, uint32_t **vals_out);
+                      uint64_t **keys_out, uint32_t **vals_out,
+                      const unsigned long long *pre_hist_d = nullptr /* [8][256] digit counts already known */,
+                      bool vals_iota = false /* values are 0..n-1: vals_a is not read */);
 
 // scan.cu
 void exclusive_scan_u32_to_u64(psc_context *ctx, const uint32_t *in, uint64_t *out, long n,
@@ -225,6 +227,7 @@ void merge_level(psc_context *ctx, const uint32_t *sa_d, const uint32_t *gap_d, 
                  const uint32_t *right_lo, const uint8_t *right_hi, long right_len,
                  uint32_t *out_lo, uint8_t *out_hi);
 void pack_sa5(psc_context *ctx, const uint32_t *lo, const uint8_t *hi, long n, uint8_t *out5);
+void pack_sa5_from_sa(psc_context *ctx, const uint32_t *sa, long n, long beg, uint8_t *out5);
 void unpack_sa5(psc_context *ctx, const uint8_t *in5, long n, uint32_t *lo, uint8_t *hi);
 void gap_to_bitvector(psc_context *ctx, const uint32_t *gap_l, long len_l, long len_r,
                       uint32_t *bv_words);

@@ -128,6 +128,43 @@ void pack_sa5(psc_context *ctx, const uint32_t *lo, const uint8_t *hi, long n, u
   ctx->launches++;
 }
 
+// single piece: beg + sa[i] straight to the 40-bit layout (no planes in between)
+__global__ void __launch_bounds__(256)
+    pack_sa32_kernel(const uint32_t *__restrict__ sa, long n, uint64_t beg, uint32_t *out_words,
+                     uint8_t *out_bytes) {
+  long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  long i = g * 4;
+  if (i >= n) return;
+  if (i + 4 <= n) {
+    uint4 s = *reinterpret_cast<const uint4 *>(sa + i);
+    uint64_t v0 = beg + s.x, v1 = beg + s.y, v2 = beg + s.z, v3 = beg + s.w;
+    uint32_t l0 = (uint32_t)v0, l1 = (uint32_t)v1, l2 = (uint32_t)v2, l3 = (uint32_t)v3;
+    uint32_t h0 = (uint32_t)(v0 >> 32) & 255, h1 = (uint32_t)(v1 >> 32) & 255, h2 = (uint32_t)(v2 >> 32) & 255,
+             h3 = (uint32_t)(v3 >> 32) & 255;
+    uint32_t *o = out_words + g * 5;
+    o[0] = l0;
+    o[1] = h0 | (l1 << 8);
+    o[2] = (l1 >> 24) | (h1 << 8) | (l2 << 16);
+    o[3] = (l2 >> 16) | (h2 << 16) | (l3 << 24);
+    o[4] = (l3 >> 8) | (h3 << 24);
+  } else {
+    for (long k = i; k < n; ++k) {
+      uint64_t v = beg + sa[k];
+      uint8_t *o = out_bytes + k * 5;
+      for (int b = 0; b < 5; ++b) o[b] = (uint8_t)(v >> (8 * b));
+    }
+  }
+}
+
+void pack_sa5_from_sa(psc_context *ctx, const uint32_t *sa, long n, long beg, uint8_t *out5) {
+  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
+  if (n <= 0) return;
+  pack_sa32_kernel<<<(unsigned)div_up(div_up(n, 4), 256), 256, 0, ctx->stream>>>(
+      sa, n, (uint64_t)beg, reinterpret_cast<uint32_t *>(out5), out5);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+}
+
 __global__ void __launch_bounds__(256)
     unpack_sa5_kernel(const uint8_t *__restrict__ in5, long n, uint32_t *__restrict__ lo,
                       uint8_t *__restrict__ hi) {

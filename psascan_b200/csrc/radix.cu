@@ -108,8 +108,14 @@ __global__ void __launch_bounds__(THREADS, MINB)
 #pragma unroll
   for (int k = 0; k < ITEMS; ++k) {
     int e = wbase + k * 32;
-    if (e < valid) { key[k] = kin[tile_beg + e]; val[k] = vin[tile_beg + e]; }
-    else { key[k] = ~0ull; val[k] = 0; }
+    key[k] = (e < valid) ? kin[tile_beg + e] : ~0ull;
+  }
+  if (vin) {
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) { int e = wbase + k * 32; val[k] = (e < valid) ? vin[tile_beg + e] : 0u; }
+  } else {  // implicit values 0..n-1 (first pass of round 0)
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) val[k] = (uint32_t)(tile_beg + wbase + k * 32);
   }
   // early counts: per-warp digit histogram (fire-and-forget shared atomics, no dependent chain)
   uint32_t *wh = warp_hist + warp * RADIX;
@@ -230,26 +236,39 @@ static const PassVariant &pass_variant() {
   return g_variants[idx];
 }
 
+__global__ void iota_kernel(uint32_t *v, long n) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) v[i] = (uint32_t)i;
+}
+
 void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint64_t *keys_b,
                       uint32_t *vals_b, long n, const int *shifts, int n_shifts,
-                      uint64_t **keys_out, uint32_t **vals_out) {
+                      uint64_t **keys_out, uint32_t **vals_out, const unsigned long long *pre_hist_d,
+                      bool vals_iota) {
   *keys_out = keys_a;
   *vals_out = vals_a;
-  if (n <= 1 || n_shifts <= 0) return;
+  if (n <= 1 || n_shifts <= 0) {
+    if (vals_iota && n > 0) { iota_kernel<<<(unsigned)div_up(n, 256), 256, 0, ctx->stream>>>(vals_a, n); PSC_LAUNCH_CHECK(); }
+    return;
+  }
   if (n_shifts > MAX_PASSES) { set_error("radix_sort_pairs: too many digit passes"); throw CudaError{PSC_EARG}; }
   PhaseTimer timer(ctx, &ctx->stats.ms_radix);
   ShiftList sl;
   sl.n = n_shifts;
   for (int p = 0; p < MAX_PASSES; ++p) sl.s[p] = p < n_shifts ? shifts[p] : 0;
 
-  DevBuf<unsigned long long> ghist(ctx, MAX_PASSES * RADIX);
-  ghist.zero();
-  int hist_blocks = (int)std::min<long>(div_up(n, 512 * 8), (long)ctx->n_sm * 4);
-  radix_hist_kernel<<<hist_blocks, 512, 0, ctx->stream>>>(keys_a, n, sl, ghist.p);
-  PSC_LAUNCH_CHECK();
-  ctx->launches++;
+  DevBuf<unsigned long long> ghist;
+  if (!pre_hist_d) {
+    ghist.alloc(ctx, MAX_PASSES * RADIX);
+    ghist.zero();
+    int hist_blocks = (int)std::min<long>(div_up(n, 512 * 8), (long)ctx->n_sm * 4);
+    radix_hist_kernel<<<hist_blocks, 512, 0, ctx->stream>>>(keys_a, n, sl, ghist.p);
+    PSC_LAUNCH_CHECK();
+    ctx->launches++;
+    pre_hist_d = ghist.p;
+  }
   std::vector<unsigned long long> h(MAX_PASSES * RADIX);
-  d2h(ctx, h.data(), ghist.p, h.size());
+  d2h(ctx, h.data(), pre_hist_d, h.size());
   sync(ctx);
 
   std::vector<uint64_t> scans(MAX_PASSES * RADIX, 0);
@@ -281,7 +300,8 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     cudaEventRecord(e0, ctx->stream);
     pv.fn<<<(unsigned)tiles, pv.threads, pv.smem, ctx->stream>>>(
-        kin, vin, kout, vout, n, sl.s[p], gscan.p + p * RADIX, status.p, counter.p);
+        kin, vals_iota ? nullptr : vin, kout, vout, n, sl.s[p], gscan.p + p * RADIX, status.p, counter.p);
+    vals_iota = false;
     cudaEventRecord(e1, ctx->stream);
     evs.push_back({e0, e1});
     PSC_LAUNCH_CHECK();
@@ -297,6 +317,10 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
     float ms = 0;
     if (cudaEventElapsedTime(&ms, e.first, e.second) == cudaSuccess) ctx->stats.ms_radix_pass += ms;
     cudaEventDestroy(e.first); cudaEventDestroy(e.second);
+  }
+  if (vals_iota) {  // every pass was skipped (all keys equal): materialise the implicit values
+    iota_kernel<<<(unsigned)div_up(n, 256), 256, 0, ctx->stream>>>(vin, n);
+    PSC_LAUNCH_CHECK();
   }
   *keys_out = kin;
   *vals_out = vin;

@@ -63,6 +63,45 @@ __global__ void __launch_bounds__(SC_THREADS)
   }
 }
 
+// one launch for both aggregate arrays of the prefix-doubling grouping: exclusive sum of `asum`
+// (total to *total_out) and exclusive running max of `amax`, 1024 threads per step
+__global__ void __launch_bounds__(1024)
+    scan_aggregates_sum_max_kernel(uint64_t *asum, uint64_t *amax, long n, uint64_t *total_out) {
+  __shared__ uint64_t ws[32], wm[32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint64_t carry_s = 0, carry_m = 0;
+  for (long base = 0; base < n; base += 1024) {
+    long i = base + threadIdx.x;
+    uint64_t vs = i < n ? asum[i] : 0, vm = i < n ? amax[i] : 0;
+    uint64_t is = vs, im = vm;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint64_t ts = __shfl_up_sync(0xffffffffu, is, o), tm = __shfl_up_sync(0xffffffffu, im, o);
+      if (lane >= o) { is += ts; im = max(im, tm); }
+    }
+    if (lane == 31) { ws[warp] = is; wm[warp] = im; }
+    __syncthreads();
+    uint64_t os = 0, om = 0, tots = 0, totm = 0;
+    for (int w = 0; w < 32; ++w) {
+      uint64_t a = ws[w], b = wm[w];
+      if (w < warp) { os += a; om = max(om, b); }
+      tots += a; totm = max(totm, b);
+    }
+    uint64_t pm = __shfl_up_sync(0xffffffffu, im, 1);
+    if (lane == 0) pm = 0;
+    if (i < n) { asum[i] = carry_s + os + is - vs; amax[i] = max(carry_m, max(om, pm)); }
+    carry_s += tots;
+    carry_m = max(carry_m, totm);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0 && total_out) *total_out = carry_s;
+}
+void scan_aggregates_sum_max(psc_context *ctx, uint64_t *asum_d, uint64_t *amax_d, long n, uint64_t *total_d) {
+  scan_aggregates_sum_max_kernel<<<1, 1024, 0, ctx->stream>>>(asum_d, amax_d, n, total_d);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+}
+
 void scan_aggregates_sum(psc_context *ctx, uint64_t *agg_d, long n, uint64_t *total_d) {
   scan_aggregates_sum_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(agg_d, n, total_d);
   PSC_LAUNCH_CHECK();

@@ -63,5 +63,6 @@ __device__ __forceinline__ T block_excl_max(T v, T *smem, T *total) {
 void scan_aggregates_sum(psc_context *ctx, uint64_t *agg_d, long n, uint64_t *total_d);
 // Single-block exclusive running max over `n` tile aggregates, in place (identity 0).
 void scan_aggregates_max(psc_context *ctx, uint64_t *agg_d, long n);
+void scan_aggregates_sum_max(psc_context *ctx, uint64_t *asum_d, uint64_t *amax_d, long n, uint64_t *total_d);
 
 }  // namespace psc

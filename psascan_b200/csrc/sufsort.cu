@@ -48,10 +48,15 @@ struct RenameLut {
 };
 
 // ---- round 0 keys --------------------------------------------------------------------------
+// keys[i] = the k renamed symbols at i, packed MSB first; also counts every 8-bit digit of the
+// keys (the radix sort's histogram), so the keys are not read again before the first pass.
 __global__ void __launch_bounds__(SC_THREADS)
     init_keys_kernel(const uint8_t *__restrict__ text, long m, const uint32_t *__restrict__ gt_end,
-                     RenameLut lut, uint64_t *__restrict__ keys, uint32_t *__restrict__ idx) {
-  extern __shared__ uint16_t codes[];  // PD_TILE + k
+                     RenameLut lut, int passes, uint64_t *__restrict__ keys,
+                     unsigned long long *__restrict__ ghist) {
+  extern __shared__ uint16_t codes[];  // PD_TILE + k, then 8 * 256 uint32 histogram
+  uint32_t *sh = reinterpret_cast<uint32_t *>(codes + ((PD_TILE + lut.k + 1) & ~1));
+  for (int e = threadIdx.x; e < 8 * 256; e += SC_THREADS) sh[e] = 0;
   const long t0 = (long)blockIdx.x * PD_TILE;
   const int span = PD_TILE + lut.k;
   for (int e = threadIdx.x; e < span; e += SC_THREADS) {
@@ -72,8 +77,11 @@ __global__ void __launch_bounds__(SC_THREADS)
     uint64_t key = 0;
     for (int s = 0; s < lut.k; ++s) key = (key << lut.bits) | codes[e + s];
     keys[i] = key;
-    idx[i] = (uint32_t)i;
+    for (int p = 0; p < passes; ++p) atomicAdd(&sh[p * 256 + (int)((key >> (8 * p)) & 255)], 1u);
   }
+  __syncthreads();
+  for (int e = threadIdx.x; e < passes * 256; e += SC_THREADS)
+    if (sh[e]) atomicAdd(&ghist[e], (unsigned long long)sh[e]);
 }
 
 // ---- grouping after a sort ------------------------------------------------------------------
@@ -293,8 +301,10 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
   DevBuf<uint64_t> keyA(ctx, m), keyB(ctx, m);
   DevBuf<uint32_t> valA(ctx, m), valB(ctx, m);
   long tiles = div_up(m, PD_TILE);
-  init_keys_kernel<<<(unsigned)tiles, SC_THREADS, (PD_TILE + k) * sizeof(uint16_t), ctx->stream>>>(
-      text_d, m, gt_end_bits_d, lut, keyA.p, valA.p);
+  DevBuf<unsigned long long> ghist(ctx, 8 * 256);
+  ghist.zero();
+  init_keys_kernel<<<(unsigned)tiles, SC_THREADS, (PD_TILE + k + 2) * sizeof(uint16_t) + 8 * 256 * 4, ctx->stream>>>(
+      text_d, m, gt_end_bits_d, lut, passes, keyA.p, ghist.p);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
   DevBuf<uint64_t> key_of_zero(ctx, 1), total_d(ctx, 1);
@@ -304,7 +314,7 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
   int shifts[8];
   for (int p = 0; p < passes; ++p) shifts[p] = 8 * p;
   uint64_t *K; uint32_t *V;
-  radix_sort_pairs(ctx, keyA.p, valA.p, keyB.p, valB.p, m, shifts, passes, &K, &V);
+  radix_sort_pairs(ctx, keyA.p, valA.p, keyB.p, valB.p, m, shifts, passes, &K, &V, ghist.p, true);
   find_i0_kernel<<<(unsigned)div_up(m, 4096), 256, 0, ctx->stream>>>(K, V, m, key_of_zero.p, i0_d.p);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
@@ -328,8 +338,7 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
     DevBuf<uint64_t> agg_act(ctx, t), agg_head(ctx, t);
     group_reduce_kernel<<<(unsigned)t, SC_THREADS, 0, ctx->stream>>>(K, a, agg_act.p, agg_head.p);
     PSC_LAUNCH_CHECK();
-    scan_aggregates_sum(ctx, agg_act.p, t, total_d.p);
-    scan_aggregates_max(ctx, agg_head.p, t);
+    scan_aggregates_sum_max(ctx, agg_act.p, agg_head.p, t, total_d.p);
     uint64_t na = 0;
     d2h(ctx, &na, total_d.p, 1);
     sync(ctx);
