@@ -1,0 +1,168 @@
+// host/psascan.hpp -- the reference's public entry point on top of the CUDA C ABI.
+//
+//   void pSAscan(std::string input_filename, std::string output_filename, std::string gap_filename,
+//                long ram_use, long max_threads, bool verbose);
+//
+// Same signature, argument meaning and error behaviour (message to stderr, std::exit(EXIT_FAILURE))
+// as /root/reference/include/psascan.hpp:137-141 and :53-131.  The text is streamed from the file to
+// the GPU through a pinned staging buffer, the whole block pipeline runs in HBM
+// (psc_construct_sa_d), and the 40-bit suffix array is streamed back to OUTFILE, so host memory use
+// is two staging buffers regardless of the text length.  ram_use bounds those buffers; the block
+// size comes from the HBM budget (psc_max_block_size) instead of ram_use / 5.2 (psascan.hpp:91),
+// or from the PSASCAN_MAX_BLOCK environment variable (testing).  gap_filename and max_threads are
+// accepted for compatibility: gap arrays never leave the device and the work runs on the GPU.
+#ifndef PSASCAN_B200_HOST_PSASCAN_HPP
+#define PSASCAN_B200_HOST_PSASCAN_HPP
+
+#include <sys/stat.h>
+#include <sys/time.h>
+#include <algorithm>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+
+#include "../include/psascan_cuda.h"
+
+namespace psascan_b200 {
+
+inline double wclock() {
+  timeval tim;
+  gettimeofday(&tim, NULL);
+  return tim.tv_sec + tim.tv_usec / 1e6;
+}
+
+inline void die_psc(const char *what) {
+  std::fprintf(stderr, "\nError: %s: %s\n", what, psc_last_error());
+  std::exit(EXIT_FAILURE);
+}
+
+inline long file_size_or_die(const std::string &fname) {
+  struct stat st;
+  if (stat(fname.c_str(), &st) != 0) {
+    std::perror(fname.c_str());  // utils.cpp:60-63 style: report and exit
+    std::exit(EXIT_FAILURE);
+  }
+  return (long)st.st_size;
+}
+
+inline void pSAscan_impl(const std::string &input_filename, const std::string &output_filename,
+                         const std::string &gap_filename, long ram_use, long max_threads, bool verbose) {
+  if (ram_use < 6L) {  // psascan.hpp:57-60
+    std::fprintf(stderr, "\nError: not enough memory to run\n");
+    std::exit(EXIT_FAILURE);
+  }
+  const long n = file_size_or_die(input_filename);
+  if (n == 0) {  // the reference cannot handle it either (gap_array.hpp:57-60)
+    std::fprintf(stderr, "\nError: the input file is empty\n");
+    std::exit(EXIT_FAILURE);
+  }
+  const double start = wclock();
+
+  psc_context *ctx = NULL;
+  if (psc_init(-1, 0, &ctx) != PSC_OK) die_psc("cannot initialise the GPU");
+  char gpu_name[128] = "";
+  size_t free_b = 0, total_b = 0;
+  psc_device_info(ctx, gpu_name, sizeof(gpu_name), &free_b, &total_b);
+
+  long max_block = psc_max_block_size(ctx, n);
+  if (const char *e = std::getenv("PSASCAN_MAX_BLOCK")) max_block = std::max(1L, std::atol(e));
+  if (max_block <= 0) {
+    std::fprintf(stderr, "\nError: text of %ld bytes does not fit the HBM budget (%.1f GiB free)\n", n,
+                 free_b / 1073741824.0);
+    std::exit(EXIT_FAILURE);
+  }
+  const long n_blocks = (n + max_block - 1) / max_block;
+  // two pinned staging buffers, each at most ram_use / 4 and at most 256 MiB
+  size_t stage = (size_t)std::max(1L << 16, std::min(256L << 20, ram_use / 4));
+
+  std::fprintf(stderr, "Input filename = %s\n", input_filename.c_str());
+  std::fprintf(stderr, "Output filename = %s\n", output_filename.c_str());
+  std::fprintf(stderr, "Gap filename = %s\n", gap_filename.c_str());
+  std::fprintf(stderr, "Input length = %ld (%.1LfMiB)\n\n", n, 1.L * n / (1 << 20));
+  std::fprintf(stderr, "GPU = %s, HBM free = %.1fGiB\n", gpu_name, free_b / 1073741824.0);
+  std::fprintf(stderr, "Host staging = 2 x %.1fMiB (RAM budget %.1LfMiB), threads = %ld (unused)\n",
+               stage / 1048576.0, 1.L * ram_use / (1 << 20), max_threads);
+  std::fprintf(stderr, "Max block size = %ld (%.1LfMiB), blocks = %ld\n\n", max_block,
+               1.L * max_block / (1 << 20), n_blocks);
+
+  void *text_d = NULL, *out_d = NULL, *pin = NULL;
+  if (psc_device_alloc(ctx, (size_t)n, &text_d) != PSC_OK) die_psc("device allocation (text)");
+  if (psc_device_alloc(ctx, 5 * (size_t)n, &out_d) != PSC_OK) die_psc("device allocation (suffix array)");
+  if (psc_pinned_alloc(ctx, stage, &pin) != PSC_OK) die_psc("pinned staging buffer");
+
+  // text: file -> pinned buffer -> HBM
+  std::FILE *f = std::fopen(input_filename.c_str(), "r");
+  if (!f) { std::perror(input_filename.c_str()); std::exit(EXIT_FAILURE); }
+  for (long done = 0; done < n;) {
+    size_t want = (size_t)std::min<long>((long)stage, n - done);
+    size_t got = std::fread(pin, 1, want, f);
+    if (got != want) {
+      std::fprintf(stderr, "\nError: fread in line %s of %s returned %ld\n", "read_text", __FILE__, (long)got);
+      std::exit(EXIT_FAILURE);
+    }
+    if (psc_copy_h2d(ctx, (char *)text_d + done, pin, got) != PSC_OK) die_psc("host to device copy");
+    done += (long)got;
+  }
+  std::fclose(f);
+
+  const double t_sa = wclock();
+  int rc = psc_construct_sa_d(ctx, (const uint8_t *)text_d, n, max_block, (uint8_t *)out_d);
+  if (rc == PSC_ESENTINEL) {  // initial_partial_sufsort.hpp:141-146 (message goes to stdout there too)
+    std::fprintf(stdout, "\n\nError: byte with value 255 was detected in the input text!\n"
+                         "See the section on limitations in the README for more information.\n");
+    std::fflush(stdout);
+    std::exit(EXIT_FAILURE);
+  }
+  if (rc != PSC_OK) die_psc("suffix array construction");
+  const double sa_time = wclock() - t_sa;
+
+  // suffix array: HBM -> pinned buffer -> file
+  std::FILE *g = std::fopen(output_filename.c_str(), "w");
+  if (!g) { std::perror(output_filename.c_str()); std::exit(EXIT_FAILURE); }
+  const size_t total = 5 * (size_t)n;
+  for (size_t done = 0; done < total;) {
+    size_t want = std::min(stage, total - done);
+    if (psc_copy_d2h(ctx, pin, (const char *)out_d + done, want) != PSC_OK) die_psc("device to host copy");
+    if (std::fwrite(pin, 1, want, g) != want) {
+      std::fprintf(stderr, "\nError: fwrite to %s failed\n", output_filename.c_str());
+      std::exit(EXIT_FAILURE);
+    }
+    done += want;
+  }
+  std::fclose(g);
+
+  if (verbose) {
+    psc_stats st;
+    psc_get_stats(ctx, &st);
+    std::fprintf(stderr,
+                 "GPU phases (ms): total %.2f | gt_end %.2f | sort %.2f (radix %.2f, %ld passes, %ld rounds) | "
+                 "bwt+gt %.2f | rank build %.2f | initial ranks %.2f | LF walk %.2f (%ld steps, %ld walkers) | "
+                 "merge %.2f | kernel launches %ld\n",
+                 st.ms_total, st.ms_gt_end, st.ms_sort, st.ms_radix, st.radix_passes, st.doubling_rounds, st.ms_bwt,
+                 st.ms_rank_build, st.ms_init_ranks, st.ms_walk, st.lf_steps, st.walkers, st.ms_merge,
+                 st.kernel_launches);
+  }
+  psc_pinned_free(ctx, pin);
+  psc_device_free(ctx, text_d);
+  psc_device_free(ctx, out_d);
+  psc_shutdown(ctx);
+
+  // summary in the reference's format (psascan.hpp:128-130)
+  const double total_time = wclock() - start;
+  std::fprintf(stderr, "\n\nComputation finished. Summary:\n");
+  std::fprintf(stderr, "  elapsed time: %.2Lfs (%.4Lfs/MiB)\n", (long double)total_time,
+               (long double)total_time / ((1.L * n) / (1L << 20)));
+  std::fprintf(stderr, "  speed: %.2LfMiB/s\n", ((1.L * n) / (1L << 20)) / (long double)total_time);
+  std::fprintf(stderr, "  GPU suffix array construction: %.3fs (%.1f MB/s)\n", sa_time, n / 1e6 / sa_time);
+}
+
+}  // namespace psascan_b200
+
+// The reference's global entry point (psascan.hpp:137-141).
+inline void pSAscan(std::string input_filename, std::string output_filename, std::string gap_filename,
+                    long ram_use, long max_threads, bool verbose) {
+  psascan_b200::pSAscan_impl(input_filename, output_filename, gap_filename, ram_use, max_threads, verbose);
+}
+
+#endif

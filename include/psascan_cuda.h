@@ -138,6 +138,16 @@ typedef struct psc_stats {
 } psc_stats;
 int psc_get_stats(psc_context *ctx, psc_stats *out);
 
+/* device / pinned-host memory for callers that stream a file through the GPU (host/psascan.hpp):
+ * the host program never links the CUDA runtime itself. */
+int psc_device_alloc(psc_context *ctx, size_t bytes, void **ptr_d);
+int psc_device_free(psc_context *ctx, void *ptr_d);
+int psc_pinned_alloc(psc_context *ctx, size_t bytes, void **ptr);
+int psc_pinned_free(psc_context *ctx, void *ptr);
+int psc_copy_h2d(psc_context *ctx, void *dst_d, const void *src, size_t bytes);
+int psc_copy_d2h(psc_context *ctx, void *dst, const void *src_d, size_t bytes);
+int psc_device_info(psc_context *ctx, char *name, size_t name_len, size_t *free_bytes, size_t *total_bytes);
+
 /* micro-benchmarks used for the roofline denominators (SURVEY.md 8-d "R32") */
 int psc_bench_random_sectors(psc_context *ctx, size_t bytes, int iters, double *gbs);
 int psc_bench_radix_pass(psc_context *ctx, long n, int iters, double *ms_per_pass);

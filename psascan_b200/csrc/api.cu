@@ -253,4 +253,50 @@ int psc_construct_sa(psc_context *ctx, const uint8_t *text, long n, long max_blo
   });
 }
 
+int psc_device_alloc(psc_context *ctx, size_t bytes, void **ptr_d) {
+  return guarded([&] {
+    arg_check(ctx && ptr_d, "psc_device_alloc");
+    PSC_CUDA(cudaSetDevice(ctx->device));
+    PSC_CUDA(cudaMalloc(ptr_d, bytes + 256));
+  });
+}
+int psc_device_free(psc_context *ctx, void *ptr_d) {
+  return guarded([&] { arg_check(ctx != nullptr, "psc_device_free"); PSC_CUDA(cudaSetDevice(ctx->device)); PSC_CUDA(cudaFree(ptr_d)); });
+}
+int psc_pinned_alloc(psc_context *ctx, size_t bytes, void **ptr) {
+  return guarded([&] { arg_check(ctx && ptr, "psc_pinned_alloc"); PSC_CUDA(cudaSetDevice(ctx->device)); PSC_CUDA(cudaMallocHost(ptr, bytes)); });
+}
+int psc_pinned_free(psc_context *ctx, void *ptr) {
+  return guarded([&] { arg_check(ctx != nullptr, "psc_pinned_free"); PSC_CUDA(cudaFreeHost(ptr)); });
+}
+int psc_copy_h2d(psc_context *ctx, void *dst_d, const void *src, size_t bytes) {
+  return guarded([&] {
+    arg_check(ctx && (bytes == 0 || (dst_d && src)), "psc_copy_h2d");
+    PSC_CUDA(cudaSetDevice(ctx->device));
+    PSC_CUDA(cudaMemcpyAsync(dst_d, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    sync(ctx);
+  });
+}
+int psc_copy_d2h(psc_context *ctx, void *dst, const void *src_d, size_t bytes) {
+  return guarded([&] {
+    arg_check(ctx && (bytes == 0 || (dst && src_d)), "psc_copy_d2h");
+    PSC_CUDA(cudaSetDevice(ctx->device));
+    PSC_CUDA(cudaMemcpyAsync(dst, src_d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    sync(ctx);
+  });
+}
+int psc_device_info(psc_context *ctx, char *name, size_t name_len, size_t *free_bytes, size_t *total_bytes) {
+  return guarded([&] {
+    arg_check(ctx != nullptr, "psc_device_info");
+    PSC_CUDA(cudaSetDevice(ctx->device));
+    cudaDeviceProp prop;
+    PSC_CUDA(cudaGetDeviceProperties(&prop, ctx->device));
+    if (name && name_len) snprintf(name, name_len, "%s", prop.name);
+    size_t f = 0, t = 0;
+    PSC_CUDA(cudaMemGetInfo(&f, &t));
+    if (free_bytes) *free_bytes = f;
+    if (total_bytes) *total_bytes = t;
+  });
+}
+
 }  // extern "C"

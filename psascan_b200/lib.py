@@ -11,7 +11,8 @@ EXPORTS = [
     "psc_sort_block", "psc_rank_build", "psc_rank_counts", "psc_rank_query", "psc_rank_free",
     "psc_initial_ranks", "psc_compute_gap", "psc_merge_level", "psc_gap_to_bitvector",
     "psc_merge_bwt", "psc_split_gap", "psc_construct_sa", "psc_construct_sa_d", "psc_get_stats",
-    "psc_bench_random_sectors", "psc_bench_radix_pass",
+    "psc_bench_random_sectors", "psc_bench_radix_pass", "psc_device_alloc", "psc_device_free",
+    "psc_pinned_alloc", "psc_pinned_free", "psc_copy_h2d", "psc_copy_d2h", "psc_device_info",
 ]
 
 

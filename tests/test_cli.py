@@ -1,0 +1,67 @@
+"""construct_sa CLI (host/construct_sa.cpp) vs the reference's command-line behaviour
+(src/main.cpp:48-246): option parsing on CPU, bit-exact .sa5 files on the GPU."""
+import os
+import subprocess
+import numpy as np
+import pytest
+from golden_cases import golden_cases, golden_text
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "host", "construct_sa")
+
+
+@pytest.fixture(scope="module")
+def cli():
+    if not os.path.exists(BIN):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "host")], stdout=subprocess.DEVNULL)
+    return BIN
+
+
+def run(cli, args, stdin=None, env=None):
+    e = dict(os.environ)
+    e.update(env or {})
+    return subprocess.run([cli] + args, input=stdin, capture_output=True, text=True, env=e)
+
+
+def test_cli_argument_errors(cli, tmp_path):
+    f = tmp_path / "t.txt"
+    f.write_bytes(b"banana")
+    r = run(cli, [])
+    assert r.returncode == 1 and "Error: FILE not provided" in r.stderr and "Usage:" in r.stdout
+    r = run(cli, ["-h"])
+    assert r.returncode == 1 and "Construct the suffix array of text stored in FILE." in r.stdout
+    r = run(cli, [str(f), "-m", "3.5gi"])
+    assert r.returncode == 1 and "Error: parsing RAM limit (3.5gi) failed" in r.stderr
+    r = run(cli, [str(f), "-m", "0"])
+    assert r.returncode == 1 and "Error: invalid RAM limit (0)" in r.stderr
+    r = run(cli, [str(tmp_path / "missing")])
+    assert r.returncode == 1 and "does not exist" in r.stderr
+    (tmp_path / "t.txt.sa5").write_bytes(b"x")
+    r = run(cli, [str(f)], stdin="n\n")
+    assert r.returncode == 1 and "exists. Overwrite? [y/n]: " in r.stdout
+    assert (tmp_path / "t.txt.sa5").read_bytes() == b"x"
+
+
+@pytest.mark.gpu
+def test_cli_bit_exact_sa5(cli, tmp_path):
+    for name, gen, kw, n, sa5 in golden_cases()[:4]:
+        f = tmp_path / (name + ".txt")
+        golden_text(gen, kw, n).tofile(str(f))
+        r = run(cli, [str(f), "-m", "3584Mi", "-v"])
+        assert r.returncode == 0, r.stderr
+        assert "Computation finished. Summary:" in r.stderr and "speed:" in r.stderr
+        assert np.array_equal(np.fromfile(str(f) + ".sa5", dtype=np.uint8), sa5)
+        out = tmp_path / (name + ".out")
+        r = run(cli, [str(f), "-o", str(out), "-g", str(tmp_path / "gap")], env={"PSASCAN_MAX_BLOCK": "1999"})
+        assert r.returncode == 0, r.stderr
+        assert np.array_equal(np.fromfile(str(out), dtype=np.uint8), sa5)
+        r = run(cli, [str(f)], stdin="y\n")  # overwrite prompt answered yes
+        assert r.returncode == 0 and "Overwrite? [y/n]" in r.stdout
+
+
+@pytest.mark.gpu
+def test_cli_rejects_255(cli, tmp_path):
+    f = tmp_path / "bad.txt"
+    f.write_bytes(b"abc\xffdef" * 50)
+    r = run(cli, [str(f)])
+    assert r.returncode == 1 and "byte with value 255 was detected in the input text!" in r.stdout
