@@ -129,6 +129,20 @@ int psc_construct_sa(psc_context *ctx, const uint8_t *text, long n, long max_blo
 int psc_construct_sa_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
                        uint8_t *out_sa5_d);
 
+/* ---- the same over several GPUs, one process per GPU.  Blocks are sorted on
+ * separate GPUs (rank r owns blocks B-1-r, B-1-r-world, ...), every GPU walks a contiguous share of
+ * the tail against a replicated rank structure, per-GPU gap counts are summed.  The collectives
+ * are delegated to the caller (NCCL through torch.distributed in psascan_b200/dist.py):
+ *   fn(user, PSC_COLL_BCAST, buf_d, bytes, root)           broadcast buf_d from rank `root`
+ *   fn(user, PSC_COLL_ALLREDUCE_SUM_U32, buf_d, bytes, 0)  element-wise uint32 sum over all ranks
+ * fn must return 0 after the operation has COMPLETED on the device.  Every rank passes the whole
+ * text and receives the whole suffix array. */
+#define PSC_COLL_BCAST 1
+#define PSC_COLL_ALLREDUCE_SUM_U32 2
+typedef int (*psc_collective_fn)(void *user, int op, void *buf_d, size_t bytes, int root);
+int psc_construct_sa_dist_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
+                            uint8_t *out_sa5_d, int rank, int world, psc_collective_fn fn, void *user);
+
 /* per-phase device time (ms, CUDA events) and counters of the last psc_construct_sa* call */
 typedef struct psc_stats {
   double ms_total, ms_gt_end, ms_sort, ms_radix, ms_bwt, ms_rank_build, ms_init_ranks, ms_walk,

@@ -1,0 +1,210 @@
+// dist.cu -- the block pipeline over several GPUs, one process per GPU.
+//
+//   phase 1  block sorts are independent once gt_end is computed by plain text comparison past the
+//            block end (no gt bits of the next block needed), so rank r sorts blocks B-1-r, B-1-r-N, ...
+//   phase 2  blocks right to left: the owner broadcasts SA, BWT and gt_begin bits of the block;
+//            every rank builds the rank structure, walks ITS contiguous share of the tail
+//            (compute_gap.hpp:68-69 splits the tail over threads the same way), and the per-GPU
+//            gap counts and gt bits are summed over NCCL; the merge level is replicated.
+// Collectives are delegated to the caller through psc_collective_fn (torch.distributed in
+// psascan_b200/dist.py, NCCL over NVLink); the library synchronises its stream around them.
+#include <algorithm>
+#include <memory>
+#include "common.cuh"
+
+namespace psc {
+
+__global__ void or_bits_shifted_kernel(uint32_t *dst, long dst_off, const uint32_t *src, long nbits) {
+  long w = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  long nw = (nbits + 31) / 32;
+  if (w >= nw) return;
+  uint32_t word = src[w];
+  long rem = nbits - w * 32;
+  if (rem < 32) word &= (1u << rem) - 1u;
+  if (!word) return;
+  long pos = dst_off + w * 32;
+  int sh = (int)(pos & 31);
+  atomicOr(&dst[pos >> 5], word << sh);
+  if (sh && (word >> (32 - sh))) atomicOr(&dst[(pos >> 5) + 1], word >> (32 - sh));
+}
+
+__global__ void set_bit_kernel(uint32_t *dst, long idx) { atomicOr(&dst[idx >> 5], 1u << (idx & 31)); }
+
+struct OwnedBlock {
+  DevBuf<uint32_t> sa;
+  DevBuf<uint8_t> bwt;
+  DevBuf<uint32_t> gtb;  // bit q <-> block position q+1, q in [0, m-1)
+  long i0 = 0;
+  int end_bit = 0;       // gt bit of position `end` relative to the block begin
+};
+
+struct BlockMeta { long long i0; int end_bit; int last; };
+
+static void coll(psc_context *ctx, psc_collective_fn fn, void *user, int op, void *buf, size_t bytes, int root) {
+  sync(ctx);
+  if (fn(user, op, buf, bytes, root) != 0) {
+    set_error("collective callback failed (op %d, %zu bytes)", op, bytes);
+    throw CudaError{PSC_ECUDA};
+  }
+}
+
+void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max_block, uint8_t *out_sa5_d,
+                       int rank, int world, psc_collective_fn fn, void *user) {
+  memset(&ctx->stats, 0, sizeof(ctx->stats));
+  ctx->launches = 0;
+  if (n == 0) return;
+  PhaseTimer total(ctx, &ctx->stats.ms_total);
+  max_block = std::min(max_block, (1L << 31) - 4096);
+  const long B = div_up(n, max_block);
+  ctx->stats.n_blocks = B;
+  auto owner = [&](long id) { return (int)((B - 1 - id) % world); };
+  auto bounds = [&](long id, long *beg, long *end) { *beg = id * max_block; *end = std::min(n, *beg + max_block); };
+
+  // ---- phase 1: my blocks, independent of each other
+  std::vector<std::unique_ptr<OwnedBlock>> mine(B);
+  for (long id = B - 1; id >= 0; --id) {
+    if (owner(id) != rank) continue;
+    long beg, end;
+    bounds(id, &beg, &end);
+    const long m = end - beg, t = n - end;
+    auto ob = std::make_unique<OwnedBlock>();
+    BlockSortResult res;
+    DevBuf<uint32_t> gt_end;
+    if (t > 0) {
+      gt_end.alloc(ctx, m / 32 + 2);
+      compute_gt_end(ctx, text_d + beg, m, text_d + end, t, 1, nullptr, 0, gt_end.p);
+    }
+    sort_block(ctx, text_d + beg, m, t > 0 ? gt_end.p : nullptr, &res);
+    res.isa.release();
+    ob->i0 = res.i0;
+    ob->gtb.alloc(ctx, m / 32 + 2);
+    ob->gtb.zero();
+    gt_begin_from_sa(ctx, res.sa.p, m, (uint32_t)res.i0, ob->gtb.p, 0);
+    uint32_t w0 = 1;  // gt_end[0]: 1 for the last block
+    if (t > 0) { d2h(ctx, &w0, gt_end.p, 1); sync(ctx); }
+    ob->end_bit = (w0 & 1u) ? 0 : 1;  // !gt_end[beg]  (change_gt_reference_point.hpp)
+    if (t > 0) {
+      ob->bwt.alloc(ctx, m);
+      bwt_from_sa(ctx, text_d + beg, res.sa.p, m, ob->bwt.p);
+    }
+    ob->sa = std::move(res.sa);
+    mine[id] = std::move(ob);
+  }
+
+  // ---- phase 2: right to left
+  const long gwords = (n + 1 + 31) / 32 + 2;
+  DevBuf<uint32_t> Ga(ctx, gwords), Gb(ctx, gwords);
+  Ga.zero(); Gb.zero();
+  uint32_t *gt_cur = Ga.p, *gt_new = Gb.p;
+  DevBuf<uint32_t> Mlo[2];
+  DevBuf<uint8_t> Mhi[2];
+  for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); Mhi[k].alloc(ctx, n); }
+  DevBuf<BlockMeta> meta_d(ctx, 1);
+  int cur = 0;
+  long right_len = 0;
+  for (long id = B - 1; id >= 0; --id) {
+    long beg, end;
+    bounds(id, &beg, &end);
+    const long m = end - beg, t = n - end;
+    const int own = owner(id);
+    OwnedBlock *ob = mine[id].get();
+    DevBuf<uint32_t> sa_tmp, gtb_tmp;
+    DevBuf<uint8_t> bwt_tmp;
+    uint32_t *sa_p, *gtb_p;
+    uint8_t *bwt_p = nullptr;
+    BlockMeta meta{0, 0, 0};
+    if (own == rank) {
+      sa_p = ob->sa.p; gtb_p = ob->gtb.p; bwt_p = ob->bwt.p;
+      uint8_t last;
+      PSC_CUDA(cudaMemcpyAsync(&last, text_d + end - 1, 1, cudaMemcpyDeviceToHost, ctx->stream));
+      sync(ctx);
+      meta = BlockMeta{ob->i0, ob->end_bit, (int)last};
+    } else {
+      sa_tmp.alloc(ctx, m); gtb_tmp.alloc(ctx, m / 32 + 2);
+      sa_p = sa_tmp.p; gtb_p = gtb_tmp.p;
+      if (t > 0) { bwt_tmp.alloc(ctx, m); bwt_p = bwt_tmp.p; }
+    }
+    if (world > 1) {
+      h2d(ctx, meta_d.p, &meta, 1);
+      coll(ctx, fn, user, PSC_COLL_BCAST, meta_d.p, sizeof(BlockMeta), own);
+      d2h(ctx, &meta, meta_d.p, 1);
+      coll(ctx, fn, user, PSC_COLL_BCAST, sa_p, (size_t)m * 4, own);
+      coll(ctx, fn, user, PSC_COLL_BCAST, gtb_p, (size_t)(m / 32 + 1) * 4, own);
+      if (t > 0) coll(ctx, fn, user, PSC_COLL_BCAST, bwt_p, (size_t)m, own);
+      sync(ctx);
+    }
+    const long i0 = (long)meta.i0;
+    PSC_CUDA(cudaMemsetAsync(gt_new, 0, gwords * 4, ctx->stream));
+    DevBuf<uint32_t> gap;
+    if (t > 0) {
+      gap.alloc(ctx, m + 1);
+      gap.zero();
+      psc_rank *rk = rank_build(ctx, bwt_p, m, i0);
+      try {
+        uint64_t Cmap[256], run = 0;
+        for (int c = 0; c < 256; ++c) { Cmap[c] = run; run += (uint64_t)rk->counts[c] + (c == meta.last ? 1 : 0); }
+        // my contiguous share of the tail, boundaries on multiples of 32
+        long per = div_up(div_up(t, (long)world), 32) * 32;
+        long lo = std::min(t, per * rank), hi = std::min(t, per * (rank + 1));
+        if (hi > lo) {
+          long target = std::max(1L, (long)ctx->n_sm * 2048);
+          long slice = std::max(64L, div_up(div_up(hi - lo, target), 32) * 32);
+          long W = div_up(hi - lo, slice);
+          std::vector<uint64_t> wb(W + 1);
+          for (long k = 0; k < W; ++k) wb[k] = (uint64_t)(lo + k * slice);
+          wb[W] = (uint64_t)hi;
+          DevBuf<uint64_t> wb_d(ctx, W + 1), sr_d(ctx, W);
+          h2d(ctx, wb_d.p, wb.data(), wb.size());
+          initial_ranks(ctx, text_d + beg, sa_p, m, text_d + end, t, 1, gt_cur, end, W, wb_d.p + 1, sr_d.p);
+          lf_walk(ctx, rk, (uint32_t)i0, (uint8_t)meta.last, Cmap, text_d + end, hi - lo, W, wb_d.p, sr_d.p, gt_cur,
+                  end, id > 0 ? gt_new : nullptr, end, gap.p);
+        }
+      } catch (...) { rank_free(rk); throw; }
+      rank_free(rk);
+      if (world > 1) {
+        coll(ctx, fn, user, PSC_COLL_ALLREDUCE_SUM_U32, gap.p, (size_t)(m + 1) * 4, 0);
+        if (id > 0) {  // disjoint bits of disjoint tail ranges: SUM == OR
+          long w0 = (end - 1) >> 5, w1 = (n >> 5) + 1;
+          coll(ctx, fn, user, PSC_COLL_ALLREDUCE_SUM_U32, gt_new + w0, (size_t)(w1 - w0) * 4, 0);
+        }
+      }
+    }
+    if (id > 0) {
+      if (m > 1) {
+        or_bits_shifted_kernel<<<(unsigned)div_up(div_up(m - 1, 32), 256), 256, 0, ctx->stream>>>(gt_new, beg, gtb_p, m - 1);
+        PSC_LAUNCH_CHECK();
+      }
+      if (meta.end_bit) { set_bit_kernel<<<1, 1, 0, ctx->stream>>>(gt_new, end - 1); PSC_LAUNCH_CHECK(); }
+      ctx->launches += 2;
+    }
+    int nxt = 1 - cur;
+    merge_level(ctx, sa_p, gap.p, m, beg, Mlo[cur].p, Mhi[cur].p, right_len, Mlo[nxt].p, Mhi[nxt].p);
+    cur = nxt;
+    right_len += m;
+    std::swap(gt_cur, gt_new);
+    sync(ctx);
+    mine[id].reset();
+  }
+  pack_sa5(ctx, Mlo[cur].p, Mhi[cur].p, n, out_sa5_d);
+  sync(ctx);
+  ctx->stats.kernel_launches = ctx->launches;
+}
+
+}  // namespace psc
+
+extern "C" int psc_construct_sa_dist_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
+                                       uint8_t *out_sa5_d, int rank, int world, psc_collective_fn fn,
+                                       void *user) {
+  try {
+    if (!ctx || n < 0 || (n > 0 && (!text_d || !out_sa5_d)) || world < 1 || rank < 0 || rank >= world ||
+        max_block <= 0 || (world > 1 && !fn)) {
+      psc::set_error("bad argument: psc_construct_sa_dist_d");
+      return PSC_EARG;
+    }
+    PSC_CUDA(cudaSetDevice(ctx->device));
+    psc::construct_sa_dist(ctx, text_d, n, max_block, out_sa5_d, rank, world, fn, user);
+    return PSC_OK;
+  } catch (const psc::CudaError &e) {
+    return e.code;
+  }
+}

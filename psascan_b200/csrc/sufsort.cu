@@ -403,13 +403,15 @@ __global__ void __launch_bounds__(256)
     gt_end_kernel(const uint8_t *__restrict__ block, long m, const uint8_t *__restrict__ after,
                   long after_len, int after_is_text_end, const uint32_t *__restrict__ gt_after,
                   long gt_after_off, uint32_t *__restrict__ out_bits) {
+  // gt_after == nullptr: the match simply continues past the block end into `after` (the block and
+  // the text after it are contiguous), so no gt bits of the next block are needed.
   long p = (long)blockIdx.x * blockDim.x + threadIdx.x;
   bool g = false;
   if (p < m) {
-    long lim = min(m - p, after_len);
+    long lim = gt_after ? min(m - p, after_len) : after_len;
     long el = common_prefix(block + p, after, lim);
     if (el == after_len && after_is_text_end) g = true;
-    else if (p + el == m) g = !bit_get(gt_after, gt_after_off + el - 1);
+    else if (gt_after && p + el == m) g = !bit_get(gt_after, gt_after_off + el - 1);
     else g = block[p + el] > after[el];
   }
   uint32_t word = __ballot_sync(0xffffffffu, g);

@@ -1,0 +1,90 @@
+"""Multi-GPU driver: one process per GPU (torch.distributed), the block pipeline of
+csrc/dist.cu with its collectives served by NCCL (or gloo on CPU buffers in the host-logic tests).
+
+Sharding: block sorts on separate GPUs, the tail walk of every block split into
+`world` contiguous shares, per-GPU gap counts summed (all-reduce over NVLink), gt bits OR-ed.
+"""
+import ctypes as C
+import numpy as np
+
+COLL_BCAST, COLL_ALLREDUCE_SUM_U32 = 1, 2
+COLLECTIVE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_int)
+
+
+def block_bounds(n, max_block):
+    """[(beg, end)] left to right, as partial_sufsort.hpp:564-570 lays blocks out."""
+    nb = -(-n // max_block)
+    return [(i * max_block, min(n, (i + 1) * max_block)) for i in range(nb)]
+
+
+def block_owner(block_id, n_blocks, world):
+    """rightmost block first: rank r owns blocks B-1-r, B-1-r-world, ... (csrc/dist.cu)"""
+    return (n_blocks - 1 - block_id) % world
+
+
+def tail_share(t, rank, world):
+    """contiguous share [lo, hi) of a tail of t symbols, boundaries on multiples of 32"""
+    per = -(-(-(-t // world)) // 32) * 32
+    return min(t, per * rank), min(t, per * (rank + 1))
+
+
+class _CudaView:
+    def __init__(self, ptr, nbytes, typestr):
+        item = int(typestr[-1])
+        self.__cuda_array_interface__ = {"shape": (nbytes // item,), "typestr": typestr, "data": (ptr, False),
+                                         "version": 3, "strides": None}
+
+
+def tensor_from_pointer(ptr, nbytes, dtype_str, cuda):
+    """zero-copy torch view of a raw buffer: dtype_str 'u1' or 'i4'"""
+    import torch
+    if cuda:
+        return torch.as_tensor(_CudaView(ptr, nbytes, "|u1" if dtype_str == "u1" else "<i4"), device="cuda")
+    ctype = C.c_uint8 if dtype_str == "u1" else C.c_int32
+    item = 1 if dtype_str == "u1" else 4
+    arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ctype)), shape=(nbytes // item,))
+    return torch.from_numpy(arr)
+
+
+def make_collective(cuda=True, group=None):
+    """the psc_collective_fn served by torch.distributed; returns (ctypes callback, call counter)"""
+    import torch
+    import torch.distributed as dist
+    counter = {"bcast": 0, "allreduce": 0, "bytes": 0}
+
+    def fn(user, op, buf, nbytes, root):
+        try:
+            if op == COLL_BCAST:
+                t = tensor_from_pointer(buf, nbytes, "u1", cuda)
+                dist.broadcast(t, src=root, group=group)
+                counter["bcast"] += 1
+            elif op == COLL_ALLREDUCE_SUM_U32:
+                # uint32 counters summed as int32: two's-complement addition is the same
+                t = tensor_from_pointer(buf, nbytes, "i4", cuda)
+                dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+                counter["allreduce"] += 1
+            else:
+                return 1
+            counter["bytes"] += nbytes
+            if cuda:
+                torch.cuda.current_stream().synchronize()
+            return 0
+        except Exception as e:  # never let an exception cross the C boundary
+            print("psascan_b200.dist collective failed:", repr(e), flush=True)
+            return 2
+
+    return COLLECTIVE_FN(fn), counter
+
+
+def construct_sa_distributed(ctx, text_dev_ptr, n, out_dev_ptr, max_block, rank=None, world=None):
+    """SPMD call: every rank passes the whole text (device pointer) and gets the whole SA."""
+    import torch.distributed as dist
+    if world is None:
+        world = dist.get_world_size() if dist.is_initialized() else 1
+        rank = dist.get_rank() if dist.is_initialized() else 0
+    cb, counter = make_collective(cuda=True)
+    f = ctx.lib.psc_construct_sa_dist_d
+    rc = f(ctx.h, C.c_void_p(text_dev_ptr), C.c_long(n), C.c_long(max_block), C.c_void_p(out_dev_ptr),
+           C.c_int(rank), C.c_int(world), cb, None)
+    ctx._chk(rc)
+    return counter

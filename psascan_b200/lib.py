@@ -12,7 +12,7 @@ EXPORTS = [
     "psc_initial_ranks", "psc_compute_gap", "psc_merge_level", "psc_gap_to_bitvector",
     "psc_merge_bwt", "psc_split_gap", "psc_construct_sa", "psc_construct_sa_d", "psc_get_stats",
     "psc_bench_random_sectors", "psc_bench_radix_pass", "psc_device_alloc", "psc_device_free",
-    "psc_pinned_alloc", "psc_pinned_free", "psc_copy_h2d", "psc_copy_d2h", "psc_device_info",
+    "psc_pinned_alloc", "psc_pinned_free", "psc_copy_h2d", "psc_copy_d2h", "psc_device_info", "psc_construct_sa_dist_d",
 ]
 
 
@@ -220,6 +220,11 @@ class Context:
         """raw-pointer variant: device=True takes device pointers (HBM-resident timing)."""
         f = self.lib.psc_construct_sa_d if device else self.lib.psc_construct_sa
         self._chk(f(self.h, C.c_void_p(text_ptr), C.c_long(n), C.c_long(max_block), C.c_void_p(out_ptr)))
+
+    def construct_sa_dist_ptr(self, text_dev_ptr, n, out_dev_ptr, max_block, rank=0, world=1, callback=None):
+        """csrc/dist.cu schedule; world == 1 needs no callback"""
+        self._chk(self.lib.psc_construct_sa_dist_d(self.h, C.c_void_p(text_dev_ptr), C.c_long(n), C.c_long(max_block),
+                                                   C.c_void_p(out_dev_ptr), C.c_int(rank), C.c_int(world), callback, None))
 
     def bench_random_sectors(self, nbytes, iters=256):
         g = C.c_double(0)

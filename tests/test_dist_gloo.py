@@ -1,0 +1,125 @@
+"""world_size-2 gloo tests (CPU) of the multi-GPU host logic: the collective adapter that serves
+the library's psc_collective_fn, and the sharding schedule of csrc/dist.cu restated with the
+oracle as the compute engine (blocks sorted on their owner, tail shares walked separately, gap
+counts summed by all-reduce, gt bits OR-ed) -- the result must be the suffix array."""
+import os
+import sys
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+sys.path.insert(0, os.path.dirname(HERE))
+
+
+def _worker(rank, world, port, q):
+    import ctypes as C
+    import oracle_lib as O
+    from psascan_b200 import dist as D, textgen
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # 1. the collective adapter on raw host pointers
+        cb, counter = D.make_collective(cuda=False)
+        buf = np.full(1000, rank + 1, dtype=np.uint32)
+        assert cb(None, D.COLL_ALLREDUCE_SUM_U32, buf.ctypes.data, buf.nbytes, 0) == 0
+        assert (buf == sum(range(1, world + 1))).all()
+        big = np.full(4, 0xF0000000, dtype=np.uint32)   # wraps like uint32 addition
+        cb(None, D.COLL_ALLREDUCE_SUM_U32, big.ctypes.data, big.nbytes, 0)
+        assert (big == np.uint32((0xF0000000 * world) & 0xFFFFFFFF)).all()
+        b = np.arange(77, dtype=np.uint8) if rank == 1 else np.zeros(77, dtype=np.uint8)
+        assert cb(None, D.COLL_BCAST, b.ctypes.data, b.nbytes, 1) == 0
+        assert (b == np.arange(77, dtype=np.uint8)).all()
+        assert counter["allreduce"] == 2 and counter["bcast"] == 1
+
+        # 2. the distributed schedule with the oracle as the engine
+        for gen, kw, n, mb in [("dna", dict(seed=3), 5000, 1300), ("periodic", dict(period=37, sigma=3), 4000, 999),
+                               ("random", dict(seed=5), 3000, 3000)]:
+            text = textgen.GENERATORS[gen](n, **kw)
+            blocks = D.block_bounds(n, mb)
+            B = len(blocks)
+            z = np.zeros(n + 2, dtype=np.uint8)
+            # phase 1: my blocks (gt_end by plain comparison = the true order, here from the full SA)
+            ref = O.sa(text)
+            isa = np.empty(n + 1, dtype=np.int64); isa[ref] = np.arange(n); isa[n] = -1
+            mine = {}
+            for bid, (beg, end) in enumerate(blocks):
+                if D.block_owner(bid, B, world) != rank:
+                    continue
+                gt_end = z.copy(); gt_end[:n + 1] = isa[:n + 1] > isa[end] if end < n else 0
+                mine[bid] = O.sort_block(text, beg, end, gt_end)
+            # phase 2
+            gt_cur = z.copy()
+            pieces = []
+            for bid in range(B - 1, -1, -1):
+                beg, end = blocks[bid]
+                m, t = end - beg, n - end
+                own = D.block_owner(bid, B, world)
+                if own == rank:
+                    psa, bwt, gtb, i0 = mine[bid]
+                    pack = [torch.from_numpy(psa.copy()), torch.from_numpy(bwt.copy()), torch.from_numpy(gtb.copy()),
+                            torch.tensor([i0])]
+                else:
+                    pack = [torch.zeros(m, dtype=torch.int64), torch.zeros(m, dtype=torch.uint8),
+                            torch.zeros(n + 2, dtype=torch.uint8), torch.zeros(1, dtype=torch.int64)]
+                for x in pack:
+                    dist.broadcast(x, src=own)
+                psa, bwt, gtb, i0 = pack[0].numpy(), pack[1].numpy(), pack[2].numpy(), int(pack[3][0])
+                gap = np.zeros(m + 1, dtype=np.int64)
+                gt_new = z.copy()
+                if t > 0:
+                    lo, hi = D.tail_share(t, rank, world)
+                    if hi > lo:
+                        start = O.initial_rank(text, beg, end, psa, end + hi, end, gt_cur)
+                        g, gout, _ = O.compute_gap(text, bwt, i0, text[end - 1], end + lo, end + hi, start, gt_cur)
+                        gap += g
+                        gt_new[end + lo + 1:end + hi + 1] = gout[end + lo + 1:end + hi + 1]
+                    gt32 = torch.from_numpy(gap.astype(np.int32))
+                    dist.all_reduce(gt32)
+                    gap = gt32.numpy().astype(np.int64)
+                    gw = torch.from_numpy(gt_new.astype(np.int32))
+                    dist.all_reduce(gw)
+                    gt_new = gw.numpy().astype(np.uint8)
+                    assert gap.sum() == t
+                gt_new[beg + 1:end + 1] |= gtb[beg + 1:end + 1]
+                pieces.append((beg, m, psa, gap))
+                gt_cur = gt_new
+            pieces.sort()
+            sa = O.merge([p[0] for p in pieces], [p[1] for p in pieces], [p[2] for p in pieces], [p[3] for p in pieces])
+            assert np.array_equal(sa, ref), (gen, rank)
+        q.put((rank, "ok"))
+    except Exception as e:
+        import traceback
+        q.put((rank, "FAIL " + traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_schedule_and_collectives():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(r[1] == "ok" for r in res), res
+
+
+def test_plan_helpers():
+    from psascan_b200 import dist as D
+    assert D.block_bounds(10, 4) == [(0, 4), (4, 8), (8, 10)]
+    assert [D.block_owner(b, 5, 2) for b in range(5)] == [0, 1, 0, 1, 0]
+    for t in (1, 31, 32, 33, 1000, 4097):
+        for w in (1, 2, 3, 8):
+            shares = [D.tail_share(t, r, w) for r in range(w)]
+            assert shares[0][0] == 0 and shares[-1][1] == t
+            for a, b in zip(shares, shares[1:]):
+                assert a[1] == b[0] and a[1] % 32 == 0 or a[1] == t

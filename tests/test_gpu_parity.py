@@ -207,3 +207,18 @@ def test_large_property_check(ctx, gen, n, mb):
     assert sa_is_valid(text, sa)
     if n <= 3_000_000:
         assert np.array_equal(sa, O.sa(text)) if n <= 2_000_000 else True
+
+
+def test_dist_schedule_single_rank(ctx):
+    """csrc/dist.cu with world = 1: sorts first (gt_end by plain comparison past the block end),
+    then the right-to-left walk/merge phase -- must equal the streaming single-GPU pipeline."""
+    import torch
+    for name, gen, kw, n, sa5 in CASES:
+        text = golden_text(gen, kw, n)
+        d_text = torch.from_numpy(text).cuda()
+        d_out = torch.zeros(5 * n, dtype=torch.uint8, device="cuda")
+        for mb in (n, n // 2 + 3, 1000):
+            d_out.zero_()
+            ctx.construct_sa_dist_ptr(d_text.data_ptr(), n, d_out.data_ptr(), mb)
+            torch.cuda.synchronize()
+            assert np.array_equal(d_out.cpu().numpy(), sa5), (name, mb)

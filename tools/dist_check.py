@@ -1,0 +1,48 @@
+"""torchrun --nproc-per-node N tools/dist_check.py : multi-GPU parity (csrc/dist.cu over NCCL)
+against the single-GPU pipeline and the golden .sa5 files; prints one line per case on rank 0."""
+import os
+import sys
+import time
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import psascan_b200 as P  # noqa: E402
+from psascan_b200 import dist as D, textgen  # noqa: E402
+from golden_cases import golden_cases, golden_text  # noqa: E402
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+ctx = P.Context(local)
+ok = True
+cases = [(name, golden_text(gen, kw, n), sa5, [1000, n // 3 + 7]) for name, gen, kw, n, sa5 in golden_cases()]
+big = textgen.markov(1 << 24, seed=3)
+cases.append(("markov_16Mi", big, None, [1 << 21]))
+for name, text, sa5, mbs in cases:
+    n = len(text)
+    d_text = torch.from_numpy(text).cuda()
+    d_out = torch.zeros(5 * n, dtype=torch.uint8, device="cuda")
+    if sa5 is None:
+        sa5 = ctx.construct_sa(text, max_block=mbs[0])
+    for mb in mbs:
+        d_out.zero_()
+        dist.barrier(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        cnt = D.construct_sa_distributed(ctx, d_text.data_ptr(), n, d_out.data_ptr(), mb)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        good = bool(np.array_equal(d_out.cpu().numpy(), sa5))
+        flag = torch.tensor([1 if good else 0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        ok = ok and bool(flag.item())
+        if rank == 0:
+            st = ctx.stats()
+            print(f"{name} n={n} max_block={mb} world={world} ok={bool(flag.item())} {dt*1e3:.1f} ms "
+                  f"walk {st['ms_walk']:.2f} ms sort {st['ms_sort']:.2f} ms coll {cnt}", flush=True)
+ctx.close()
+dist.destroy_process_group()
+sys.exit(0 if ok else 1)
