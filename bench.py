@@ -31,8 +31,8 @@ WORKLOADS = {
     "random1g": ("random", dict(seed=2), 1 << 30, 0,
                  "configs[1]: 1 GiB uniform-random bytes (sigma=255), single block in HBM"),
     "dna200m": ("dna", dict(seed=1), 200_000_000, 0, "configs[0]: 200 MB DNA-like (sigma=4), single block"),
-    "markov_multi": ("markov", dict(seed=3), 1 << 28, 1 << 25,
-                     "configs[2] scaled: order-5 Markov text, 8 blocks, gap streaming"),
+    "markov_multi": ("markov", dict(seed=3), 1 << 30, 1 << 27,
+                     "configs[2] scaled 1/16: 1 GiB order-5 Markov text, 8 blocks of 128 MiB, gap streaming"),
     "repetitive_multi": ("repetitive", dict(seed=4), 1 << 28, 1 << 26,
                          "configs[3] scaled: mutated copies of a 1 MiB seed, 4 blocks"),
 }
@@ -50,6 +50,10 @@ def gen_text(workload, size, rank):
         rng = np.random.default_rng(kw["seed"])
         t = rng.integers(0, 255, size=n, dtype=np.uint8)
         return t, (mb if mb < n else 0)
+    if gen == "markov" and n >= (1 << 26):
+        import torch
+        if torch.cuda.is_available():   # GiB-sized Markov texts are generated on the GPU (same model)
+            return textgen.markov_torch(n, seed=kw["seed"]).cpu().numpy(), (mb if mb < n else 0)
     return textgen.GENERATORS[gen](n, **kw), (mb if mb < n else 0)
 
 
@@ -188,12 +192,31 @@ def main():
     dev_text = host_text.cuda()
     dev_out = torch.empty(5 * n, dtype=torch.uint8, device="cuda")
 
+    sharded = world > 1 and max_block > 0   # multi-block workload: csrc/dist.cu over NCCL (strong scaling)
+    if sharded:
+        from psascan_b200 import dist as pdist
+        if rank != 0:   # every rank must hold the same text
+            text, _ = gen_text(a.workload, n, 0)
+            host_text.copy_(torch.from_numpy(text))
+            dev_text.copy_(host_text)
+
     def step_dev():
-        ctx.construct_sa_ptr(dev_text.data_ptr(), n, dev_out.data_ptr(), max_block, device=True)
+        if sharded:
+            pdist.construct_sa_distributed(ctx, dev_text.data_ptr(), n, dev_out.data_ptr(), max_block)
+        else:
+            ctx.construct_sa_ptr(dev_text.data_ptr(), n, dev_out.data_ptr(), max_block, device=True)
         return ctx.stats()
 
     def step_e2e():
-        ctx.construct_sa_ptr(host_text.data_ptr(), n, host_out.data_ptr(), max_block, device=False)
+        if sharded:   # host text -> HBM on every rank, sharded construction, SA back to rank 0's host
+            dev_text.copy_(host_text, non_blocking=True)
+            torch.cuda.synchronize()
+            pdist.construct_sa_distributed(ctx, dev_text.data_ptr(), n, dev_out.data_ptr(), max_block)
+            if rank == 0:
+                host_out.copy_(dev_out, non_blocking=True)
+            torch.cuda.synchronize()
+        else:
+            ctx.construct_sa_ptr(host_text.data_ptr(), n, host_out.data_ptr(), max_block, device=False)
         return ctx.stats()
 
     for _ in range(a.warmup):
@@ -225,7 +248,7 @@ def main():
     sa_sum = int(psascan_b200.lib.decode_sa5(host_out.numpy()[: 5 * min(n, 1 << 20)]).sum()) if n else 0
     if rank == 0:
         s = stats[-1]
-        total_bytes = n * world
+        total_bytes = n if sharded else n * world
         value = total_bytes * a.steps / 1e6 / (dev_ms / 1e3)
         e2e = total_bytes * a.steps / 1e6 / (e2e_ms / 1e3)
         peak, peak_src = measured_peaks()
@@ -234,6 +257,12 @@ def main():
                     "achieved": 41.25 * s["lf_steps"] / (s["ms_walk"] / 1e3) / 1e9,
                     "algorithmic_bytes_per_unit": 41.25, "units": "LF steps", "peak": peak, "peak_source": peak_src,
                     "lf_steps_per_s": s["lf_steps"] / (s["ms_walk"] / 1e3), "traffic": None}
+            try:   # random 32-byte sector rate of this GPU (SURVEY 8-d "R32"), the walk's real ceiling
+                r32 = ctx.bench_random_sectors(8 << 30, 128)
+                roof["r32_gbs"] = r32
+                roof["frac_of_r32"] = roof["achieved"] / r32
+            except Exception as e:
+                roof["r32_error"] = str(e)[:100]
         else:
             roof = {"kernel": "radix_pass_kernel", "bound": "hbm", "unit": "GB/s",
                     "achieved": 24.0 * s["radix_elems"] / (s["ms_radix_pass"] / 1e3) / 1e9 if s["ms_radix_pass"] else None,
@@ -245,8 +274,11 @@ def main():
             roof["frac"] = roof["achieved"] / peak
         line = {"metric": "SA construction input MB/s", "value": value, "unit": "MB/s", "n_gpus": world,
                 "steps": a.steps, "warmup": a.warmup, "ms_per_step": dev_ms / a.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "u8 text, u64 keys, u32 ranks", "data": "synthetic",
-                "config": dict(config, parallelism="replicas" if world > 1 else "single GPU", max_block=max_block),
+                "scaling": "strong" if sharded else "weak", "vs_baseline": None,
+                "dtype": "u8 text, u64 keys, u32 ranks", "data": "synthetic",
+                "config": dict(config, parallelism=("block sorts per GPU + sharded tail walk + NCCL all-reduce of gap counts"
+                                                    if sharded else "replicas" if world > 1 else "single GPU"),
+                               max_block=max_block),
                 "clocks": clocks, "wall_ms_per_step": wall_ms / a.steps,
                 "e2e": {"value": e2e, "unit": "MB/s", "h2d_bytes_per_step": n, "d2h_bytes_per_step": 5 * n,
                         "ms_per_step": e2e_ms / a.steps},

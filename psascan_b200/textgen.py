@@ -26,13 +26,13 @@ def markov(n: int, seed: int = 3, order: int = 5, rows_log: int = 20) -> np.ndar
     2^rows_log rows; each row has a Zipf(1.2) distribution over 8 symbols picked by a hash
     of the row.  Generated as 4096 independent lanes advanced in lock-step so numpy can
     vectorise it; lane l owns text[l*L:(l+1)*L]."""
-    lanes = 4096 if n >= (1 << 16) else 1
+    lanes = (1 << 16) if n >= (1 << 24) else (4096 if n >= (1 << 16) else 1)
     per = -(-n // lanes)
     rng = np.random.default_rng(seed)
     w = 1.0 / np.arange(1, 9) ** 1.2
     cdf = np.cumsum(w / w.sum())
     cdf[-1] = 1.0
-    out = np.empty((lanes, per), dtype=np.uint8)
+    out = np.empty((per, lanes), dtype=np.uint8)   # row t = symbol t of every lane
     ctx = rng.integers(0, 1 << 62, size=lanes, dtype=np.uint64)
     mask = np.uint64((1 << (5 * order)) - 1)
     rmask = np.uint64((1 << rows_log) - 1)
@@ -46,9 +46,9 @@ def markov(n: int, seed: int = 3, order: int = 5, rows_log: int = 20) -> np.ndar
         h = (row ^ sd) * mul + k * np.uint64(0xBF58476D1CE4E5B9)
         h ^= h >> np.uint64(31)
         sym = (h % np.uint64(30)).astype(np.uint8)
-        out[:, t] = _MARKOV_ALPHA[sym]
+        out[t] = _MARKOV_ALPHA[sym]
         ctx = (ctx << np.uint64(5)) | sym.astype(np.uint64)
-    return out.reshape(-1)[:n].copy()
+    return np.ascontiguousarray(out.T).reshape(-1)[:n].copy()
 
 
 def repetitive(n: int, seed: int = 4, seed_len: int = 1 << 20, rate: float = 1e-3) -> np.ndarray:
@@ -74,3 +74,33 @@ def periodic(n: int, period: int = 997, sigma: int = 3, seed: int = 7) -> np.nda
 
 GENERATORS = {"dna": dna, "random": random_bytes, "markov": markov,
               "repetitive": repetitive, "periodic": periodic}
+
+
+def markov_torch(n: int, seed: int = 3, order: int = 5, rows_log: int = 20, device="cuda"):
+    """same model as markov(), generated with torch on `device` (bench inputs of GiB size; the
+    stream differs from the numpy generator's, the statistics do not)."""
+    import torch
+    lanes = 1 << 20 if n >= (1 << 26) else 1 << 14
+    per = -(-n // lanes)
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    w = 1.0 / torch.arange(1, 9, dtype=torch.float64) ** 1.2
+    cdf = torch.cumsum(w / w.sum(), 0).to(device=device, dtype=torch.float32)
+    cdf[-1] = 2.0
+    alpha = torch.from_numpy(_MARKOV_ALPHA.copy()).to(device)
+    out = torch.empty((per, lanes), dtype=torch.uint8, device=device)
+    ctx = torch.randint(0, 1 << 62, (lanes,), generator=g, device=device, dtype=torch.int64)
+    mask = (1 << (5 * order)) - 1
+    rmask = (1 << rows_log) - 1
+    mul = -7046029254386353131          # 0x9E3779B97F4A7C15 as int64
+    mul2 = -4658895280553007687         # 0xBF58476D1CE4E5B9 as int64
+    for t in range(per):
+        row = (((ctx & mask) * mul) >> 40) & rmask
+        u = torch.rand(lanes, generator=g, device=device)
+        k = torch.searchsorted(cdf, u).to(torch.int64)
+        h = (row ^ seed) * mul + k * mul2
+        h = h ^ ((h >> 31) & 0x1FFFFFFFF)
+        sym = torch.remainder(h, 30)
+        out[t] = alpha[sym]
+        ctx = (ctx << 5) | sym
+    return out.t().contiguous().reshape(-1)[:n]
