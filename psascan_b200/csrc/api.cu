@@ -70,7 +70,7 @@ static void gap_of_block(psc_context *ctx, const uint8_t *block_d, long m, const
     h2d(ctx, wb_d.p, wb.data(), wb.size());
     // walker k starts from the rank of suffix(after + wb[k+1]); the last one from suffix(n): 0
     initial_ranks(ctx, block_d, sa_d, m, after_d, t, 1, gt_cur, gt_off, W, wb_d.p + 1, sr_d.p);
-    lf_walk(ctx, rk, (uint32_t)i0, last, Cmap, after_d, t, W, wb_d.p, sr_d.p, gt_cur, gt_off, gt_new,
+    lf_walk(ctx, rk, (uint32_t)i0, last, Cmap, after_d, t, 0, W, wb_d.p, sr_d.p, gt_cur, gt_off, gt_new,
             gt_off, gap_d);
     sync(ctx);
   } catch (...) {

@@ -181,7 +181,7 @@ int psc_compute_gap(psc_context *ctx, const psc_rank *rank, long i0, uint8_t las
     DevBuf<uint64_t> wb_d(ctx, nwalk + 1), sr_d(ctx, nwalk);
     h2d(ctx, wb_d.p, wb.data(), nwalk + 1);
     h2d(ctx, sr_d.p, sr.data(), nwalk);
-    lf_walk(ctx, rank, (uint32_t)i0, last, Cmap, tail_d.p, t, nwalk, wb_d.p, sr_d.p, gin.p, 0,
+    lf_walk(ctx, rank, (uint32_t)i0, last, Cmap, tail_d.p, t, 0, nwalk, wb_d.p, sr_d.p, gin.p, 0,
             gt_out_rev ? gout.p : nullptr, 0, gap_d.p);
     d2h(ctx, gap, gap_d.p, m + 1);
     sync(ctx);

@@ -216,9 +216,9 @@ void initial_ranks(psc_context *ctx, const uint8_t *block_d, const uint32_t *sa_
                    const uint32_t *gt_after_bits_d, long gt_after_off, long nstarts,
                    const uint64_t *starts_d, uint64_t *out_d);
 // K6: LF walk.  Cmap[c] = number of block symbols < c.  gt bits forward over the tail:
-// bit q <-> tail position q+1.
+// bit q <-> tail position q+1.  The walkers cover tail positions [lo, lo+t).
 void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, const uint64_t *Cmap,
-             const uint8_t *tail_d, long t, long nwalk, const uint64_t *walk_beg_d,
+             const uint8_t *tail_d, long t, long lo, long nwalk, const uint64_t *walk_beg_d,
              const uint64_t *start_rank_d, const uint32_t *gt_in_bits_d, long gt_in_off,
              uint32_t *gt_out_bits_d, long gt_out_off, uint32_t *gap_d);
 

@@ -156,7 +156,7 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
           DevBuf<uint64_t> wb_d(ctx, W + 1), sr_d(ctx, W);
           h2d(ctx, wb_d.p, wb.data(), wb.size());
           initial_ranks(ctx, text_d + beg, sa_p, m, text_d + end, t, 1, gt_cur, end, W, wb_d.p + 1, sr_d.p);
-          lf_walk(ctx, rk, (uint32_t)i0, (uint8_t)meta.last, Cmap, text_d + end, hi - lo, W, wb_d.p, sr_d.p, gt_cur,
+          lf_walk(ctx, rk, (uint32_t)i0, (uint8_t)meta.last, Cmap, text_d + end, hi - lo, lo, W, wb_d.p, sr_d.p, gt_cur,
                   end, id > 0 ? gt_new : nullptr, end, gap.p);
         }
       } catch (...) { rank_free(rk); throw; }

@@ -15,15 +15,22 @@ constexpr int MG_ITEMS = 8;
 constexpr int MG_TILE = SC_THREADS * MG_ITEMS;  // outputs per block
 
 // E[0..m] exclusive scan of gap[0..m];  A(u) = u + E[u] = output slot where run u starts
-// (run u = gap[u] entries of `right`, then the block's u-th suffix when u < m).
+// (run u = gap[u] entries of `right`, then the block's u-th suffix at slot A(u+1)-1 when u < m).
+// Per tile of MG_TILE output slots: one binary search finds u0 = the run the tile starts in, the
+// slots taken by block suffixes are marked in a shared bitmap (they belong to u0, u0+1, ... in
+// order), and a prefix popcount turns every slot into either "block suffix u0+k" or "entry
+// q-(u0+k) of the right side".  O(1) work per slot, all global accesses coalesced.
 __global__ void __launch_bounds__(SC_THREADS)
     merge_level_kernel(const uint32_t *__restrict__ sa, const uint64_t *__restrict__ E, long m,
                        uint64_t beg, const uint32_t *__restrict__ right_lo,
                        const uint8_t *__restrict__ right_hi, long total,
                        uint32_t *__restrict__ out_lo, uint8_t *__restrict__ out_hi) {
-  __shared__ uint64_t sA[MG_TILE + 2];
+  constexpr int WORDS = MG_TILE / 32;
+  __shared__ uint32_t flags[WORDS];
+  __shared__ uint32_t before[WORDS];
   __shared__ long s_u0;
   const long q0 = (long)blockIdx.x * MG_TILE;
+  if (threadIdx.x < WORDS) flags[threadIdx.x] = 0;
   if (threadIdx.x == 0) {
     // largest u in [0, m] with u + E[u] <= q0
     long lo = 0, hi = m;
@@ -35,26 +42,38 @@ __global__ void __launch_bounds__(SC_THREADS)
   }
   __syncthreads();
   const long u0 = s_u0;
-  const long cnt = min((long)MG_TILE + 2, m + 1 - u0);  // A(u0 .. u0+cnt-1)
-  for (long e = threadIdx.x; e < cnt; e += SC_THREADS) sA[e] = (uint64_t)(u0 + e) + E[u0 + e];
+  // block suffix u sits at slot u + E[u+1]; only u0 .. u0+MG_TILE-1 can fall into this tile
+  for (long e = threadIdx.x; e < MG_TILE; e += SC_THREADS) {
+    long u = u0 + e;
+    if (u >= m) break;
+    uint64_t p = (uint64_t)u + E[u + 1];
+    if (p >= (uint64_t)q0 + MG_TILE) break;
+    if (p >= (uint64_t)q0) atomicOr(&flags[(p - q0) >> 5], 1u << ((p - q0) & 31));
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {  // exclusive prefix popcount over the WORDS flag words
+    uint32_t run = 0;
+    for (int w0 = 0; w0 < WORDS; w0 += 32) {
+      uint32_t c = __popc(flags[w0 + threadIdx.x]), incl = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (threadIdx.x >= o) incl += t; }
+      before[w0 + threadIdx.x] = run + incl - c;
+      run += __shfl_sync(0xffffffffu, incl, 31);
+    }
+  }
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < MG_ITEMS; ++k) {
-    long q = q0 + threadIdx.x + (long)k * SC_THREADS;
+    int i = threadIdx.x + k * SC_THREADS;
+    long q = q0 + i;
     if (q >= total) break;
-    // largest e in [0, cnt) with sA[e] <= q
-    long lo = 0, hi = min(cnt - 1, q - q0 + 0L);
-    // A(u0 + e) >= q0 + e is not guaranteed for e = 0 only (A(u0) <= q0), so hi = q - q0 is safe
-    while (lo < hi) {
-      long mid = (lo + hi + 1) >> 1;
-      if (sA[mid] <= (uint64_t)q) lo = mid; else hi = mid - 1;
-    }
-    long u = u0 + lo;
+    uint32_t word = flags[i >> 5];
+    uint32_t nb = before[i >> 5] + __popc(word & ((1u << (i & 31)) - 1u));
     uint64_t v;
-    if (u < m && lo + 1 < cnt && sA[lo + 1] - 1 == (uint64_t)q) {
-      v = beg + sa[u];
+    if ((word >> (i & 31)) & 1u) {
+      v = beg + sa[u0 + nb];
     } else {
-      uint64_t r = (uint64_t)(q - u);  // u block suffixes precede slot q, the rest come from `right`
+      uint64_t r = (uint64_t)q - (uint64_t)(u0 + nb);  // block suffixes before slot q: u0 + nb
       v = (uint64_t)right_lo[r] | ((uint64_t)right_hi[r] << 32);
     }
     out_lo[q] = (uint32_t)v;

@@ -217,6 +217,8 @@ struct PassVariant { const char *name; PassFn fn; int threads, tile; size_t smem
 static const PassVariant g_variants[] = {
     PASS_VARIANT(512, 12, 2, 0), PASS_VARIANT(384, 12, 3, 0), PASS_VARIANT(512, 8, 3, 0), PASS_VARIANT(512, 16, 2, 0),
     PASS_VARIANT(256, 12, 4, 0), PASS_VARIANT(1024, 8, 1, 0), PASS_VARIANT(512, 12, 2, 12),
+    PASS_VARIANT(256, 12, 5, 0), PASS_VARIANT(256, 8, 6, 0), PASS_VARIANT(384, 8, 4, 0), PASS_VARIANT(256, 16, 3, 0),
+    PASS_VARIANT(128, 12, 8, 0), PASS_VARIANT(256, 8, 8, 0),
 };
 static const PassVariant &pass_variant() {
   static int idx = -1;

@@ -60,17 +60,30 @@ struct WalkTables {
   int16_t code[256];   // dense code in the rank structure, -1 = symbol absent from the BWT
 };
 
-template <bool AGG>
+// How the ranks reach the gap array.  Measured on B200 (1 GiB Markov text, 128 MiB blocks): the
+// walk alone runs at 38.7 G steps/s = the random 32-byte sector rate of HBM; a RED per step on a
+// 512 MB gap array (one more random sector read + write-back) drops it to 14.6 G steps/s.  So for
+// gap arrays larger than L2 the ranks are streamed out, partitioned by their high bits into
+// buckets whose counter range (16 MB) stays in L2, and only then counted: 16 B of sequential
+// traffic per step instead of 64 B of random traffic.  (The reference partitions its gap buffers
+// by value range for another reason -- lock-free CPU updaters, stream.hpp:160-232.)
+//   MODE 0: RED on gap[i]   1: warp-aggregated RED (match.any)   2: emit ranks + bucket counts
+constexpr int WK_MAX_BUCKETS = 512;
+
+template <int MODE>
 __global__ void __launch_bounds__(256)
     lf_walk_kernel(RankView rv, uint32_t i0, int last, const WalkTables *__restrict__ tables,
                    const uint8_t *__restrict__ tail, long nwalk, const uint64_t *__restrict__ walk_beg,
                    const uint64_t *__restrict__ start_rank, const uint32_t *__restrict__ gt_in,
                    long gt_in_off, uint32_t *__restrict__ gt_out, long gt_out_off,
-                   uint32_t *__restrict__ gap) {
+                   uint32_t *__restrict__ gap, uint32_t *__restrict__ emit, long emit_base, int bshift,
+                   int n_buckets, unsigned long long *__restrict__ bucket_count) {
   __shared__ uint32_t sC[256];
   __shared__ int16_t sCode[256];
+  __shared__ uint32_t sB[MODE == 2 ? WK_MAX_BUCKETS : 1];
   sC[threadIdx.x] = tables->C[threadIdx.x];
   sCode[threadIdx.x] = tables->code[threadIdx.x];
+  if (MODE == 2) for (int b = threadIdx.x; b < n_buckets; b += 256) sB[b] = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31;
   long w = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -115,7 +128,12 @@ __global__ void __launch_bounds__(256)
       i = sC[c] + occ + ((c == last) ? gin : 0u);
       --j;
     }
-    if (AGG) {
+    if (MODE == 2) {
+      if (active) {
+        emit[j - emit_base] = i;  // the rank of suffix tail+j, at the slot of position j
+        atomicAdd(&sB[i >> bshift], 1u);
+      }
+    } else if (MODE == 1) {
       uint32_t peers = __match_any_sync(0xffffffffu, active ? i : (0xffffffffu - lane));
       if (active && lane == __ffs(peers) - 1) atomicAdd(&gap[i], (uint32_t)__popc(peers));
     } else {
@@ -123,12 +141,87 @@ __global__ void __launch_bounds__(256)
     }
   }
   if (gt_out && cur_out_w >= 0 && out_word) atomicOr(&gt_out[cur_out_w], out_word);
+  if (MODE == 2) {
+    __syncthreads();
+    for (int b = threadIdx.x; b < n_buckets; b += 256)
+      if (sB[b]) atomicAdd(&bucket_count[b], (unsigned long long)sB[b]);
+  }
+}
+
+// ranks -> buckets (order inside a bucket is irrelevant: they are only counted afterwards)
+constexpr int PT_THREADS = 512;
+constexpr int PT_ITEMS = 16;
+constexpr int PT_TILE = PT_THREADS * PT_ITEMS;  // 8192 ranks, 32 KB of staging
+
+__global__ void __launch_bounds__(PT_THREADS)
+    rank_partition_kernel(const uint32_t *__restrict__ in, long n, int bshift, int n_buckets,
+                          unsigned long long *__restrict__ cursor, uint32_t *__restrict__ out) {
+  __shared__ uint32_t cnt[WK_MAX_BUCKETS];    // count, then running slot inside the tile
+  __shared__ uint32_t toff[WK_MAX_BUCKETS];   // first slot of the bucket inside the tile
+  __shared__ unsigned long long gofs[WK_MAX_BUCKETS];
+  __shared__ uint32_t stage[PT_TILE];
+  __shared__ uint32_t wsum[PT_THREADS / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long base = (long)blockIdx.x * PT_TILE;
+  const int valid = (int)min((long)PT_TILE, n - base);
+  for (int b = tid; b < n_buckets; b += PT_THREADS) cnt[b] = 0;
+  __syncthreads();
+  uint32_t v[PT_ITEMS];
+#pragma unroll
+  for (int k = 0; k < PT_ITEMS; ++k) {
+    int e = tid + k * PT_THREADS;
+    v[k] = e < valid ? in[base + e] : 0xffffffffu;
+    if (e < valid) atomicAdd(&cnt[v[k] >> bshift], 1u);
+  }
+  __syncthreads();
+  // exclusive scan of the bucket counts (one bucket per thread), reserve global space
+  static_assert(WK_MAX_BUCKETS <= PT_THREADS, "one bucket per thread");
+  {
+    uint32_t c = tid < n_buckets ? cnt[tid] : 0u, incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    uint32_t woff = 0;
+    for (int w = 0; w < warp; ++w) woff += wsum[w];
+    uint32_t ex = woff + incl - c;
+    if (tid < n_buckets) {
+      toff[tid] = ex; cnt[tid] = ex;
+      if (c) gofs[tid] = atomicAdd(&cursor[tid], (unsigned long long)c);
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < PT_ITEMS; ++k) {
+    int e = tid + k * PT_THREADS;
+    if (e < valid) stage[atomicAdd(&cnt[v[k] >> bshift], 1u)] = v[k];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < PT_ITEMS; ++k) {
+    int e = tid + k * PT_THREADS;
+    if (e < valid) {
+      uint32_t x = stage[e];
+      int b = (int)(x >> bshift);
+      out[gofs[b] + (unsigned long long)(e - toff[b])] = x;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    rank_accumulate_kernel(const uint32_t *__restrict__ in, long n, uint32_t *__restrict__ gap) {
+  long i = ((long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i + 4 <= n) {
+    uint4 x = *reinterpret_cast<const uint4 *>(in + i);
+    atomicAdd(&gap[x.x], 1u); atomicAdd(&gap[x.y], 1u); atomicAdd(&gap[x.z], 1u); atomicAdd(&gap[x.w], 1u);
+  } else {
+    for (; i < n; ++i) atomicAdd(&gap[in[i]], 1u);
+  }
 }
 
 void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, const uint64_t *Cmap,
-             const uint8_t *tail_d, long t, long nwalk, const uint64_t *walk_beg_d,
-             const uint64_t *start_rank_d, const uint32_t *gt_in_bits_d, long gt_in_off,
-             uint32_t *gt_out_bits_d, long gt_out_off, uint32_t *gap_d) {
+             const uint8_t *tail_d, long t, long lo, long nwalk, const uint64_t *walk_beg_d, const uint64_t *start_rank_d, const uint32_t *gt_in_bits_d,
+             long gt_in_off, uint32_t *gt_out_bits_d, long gt_out_off, uint32_t *gap_d) {
   PhaseTimer timer(ctx, &ctx->stats.ms_walk);
   if (nwalk <= 0 || t <= 0) return;
   WalkTables tb;
@@ -136,20 +229,50 @@ void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, con
   DevBuf<WalkTables> tb_d(ctx, 1);
   h2d(ctx, tb_d.p, &tb, 1);
   RankView rv{r->sectors_d, r->n_sectors, (uint32_t)r->m};
-  static int agg = -1;
-  if (agg < 0) { const char *e = getenv("PSC_WALK_AGG"); agg = e ? atoi(e) : 0; }
+  static int mode = -2;
+  if (mode == -2) { const char *e = getenv("PSC_WALK_MODE"); mode = e ? atoi(e) : -1; }
+  const long hi = lo + t;  // the walkers cover tail positions [lo, hi)
+  int use = mode;
+  if (use < 0) use = ((size_t)(r->m + 1) * 4 > (size_t)(24 << 20) && hi - lo >= (1 << 20)) ? 2 : 0;
   unsigned blocks = (unsigned)div_up(nwalk, 256);
-  if (agg)
-    lf_walk_kernel<true><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d,
-                                                           start_rank_d, gt_in_bits_d, gt_in_off,
-                                                           gt_out_bits_d, gt_out_off, gap_d);
-  else
-    lf_walk_kernel<false><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d,
-                                                            start_rank_d, gt_in_bits_d, gt_in_off,
-                                                            gt_out_bits_d, gt_out_off, gap_d);
-  PSC_LAUNCH_CHECK();
-  sync(ctx);  // tb is a stack object
-  ctx->launches++;
+  if (use == 2) {
+    const long T = hi - lo;
+    int bshift = 22;  // 4 Mi counters = 16 MB of gap array per bucket
+    while (((r->m + 1) >> bshift) + 1 > WK_MAX_BUCKETS) ++bshift;
+    const int nb = (int)(((r->m + 1) >> bshift) + 1);
+    DevBuf<uint32_t> emit(ctx, T), part(ctx, T);
+    DevBuf<unsigned long long> bc(ctx, WK_MAX_BUCKETS), cur(ctx, WK_MAX_BUCKETS);
+    bc.zero();
+    lf_walk_kernel<2><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d, start_rank_d,
+                                                        gt_in_bits_d, gt_in_off, gt_out_bits_d, gt_out_off, gap_d,
+                                                        emit.p, lo, bshift, nb, bc.p);
+    PSC_LAUNCH_CHECK();
+    unsigned long long h[WK_MAX_BUCKETS], c[WK_MAX_BUCKETS];
+    d2h(ctx, h, bc.p, nb);
+    sync(ctx);
+    unsigned long long run = 0;
+    for (int b = 0; b < nb; ++b) { c[b] = run; run += h[b]; }
+    h2d(ctx, cur.p, c, nb);
+    rank_partition_kernel<<<(unsigned)div_up(T, PT_TILE), PT_THREADS, 0, ctx->stream>>>(emit.p, T, bshift, nb, cur.p,
+                                                                                      part.p);
+    PSC_LAUNCH_CHECK();
+    rank_accumulate_kernel<<<(unsigned)div_up(div_up(T, 4), 256), 256, 0, ctx->stream>>>(part.p, T, gap_d);
+    PSC_LAUNCH_CHECK();
+    sync(ctx);
+    ctx->launches += 3;
+  } else {
+    if (use == 1)
+      lf_walk_kernel<1><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d, start_rank_d,
+                                                          gt_in_bits_d, gt_in_off, gt_out_bits_d, gt_out_off, gap_d,
+                                                          nullptr, 0, 0, 0, nullptr);
+    else
+      lf_walk_kernel<0><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d, start_rank_d,
+                                                          gt_in_bits_d, gt_in_off, gt_out_bits_d, gt_out_off, gap_d,
+                                                          nullptr, 0, 0, 0, nullptr);
+    PSC_LAUNCH_CHECK();
+    sync(ctx);  // tb is a stack object
+    ctx->launches++;
+  }
   ctx->stats.lf_steps += t;
   ctx->stats.walkers = nwalk;
 }
