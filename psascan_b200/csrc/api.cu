@@ -170,6 +170,12 @@ int psc_init(int device, size_t hbm_budget, psc_context **out) {
     }
     if (device < 0) PSC_CUDA(cudaGetDevice(&device));
     PSC_CUDA(cudaSetDevice(device));
+    if (const char *e = getenv("PSC_L2_FETCH")) {
+      size_t got = 0;
+      cudaError_t rc = cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));
+      cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity);
+      fprintf(stderr, "[psc] L2 fetch granularity: set %s -> %s, now %zu\n", e, cudaGetErrorName(rc), got);
+    }
     psc_context *c = new psc_context();
     c->device = device;
     cudaDeviceProp prop;

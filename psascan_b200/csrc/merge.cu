@@ -16,32 +16,36 @@ constexpr int MG_TILE = SC_THREADS * MG_ITEMS;  // outputs per block
 
 // E[0..m] exclusive scan of gap[0..m];  A(u) = u + E[u] = output slot where run u starts
 // (run u = gap[u] entries of `right`, then the block's u-th suffix at slot A(u+1)-1 when u < m).
-// Per tile of MG_TILE output slots: one binary search finds u0 = the run the tile starts in, the
+// Per tile of MG_TILE output slots: u0 = the run the tile starts in (one binary search per tile,
+// all tiles searched in parallel by merge_tile_start_kernel so the dependent loads overlap), the
 // slots taken by block suffixes are marked in a shared bitmap (they belong to u0, u0+1, ... in
 // order), and a prefix popcount turns every slot into either "block suffix u0+k" or "entry
 // q-(u0+k) of the right side".  O(1) work per slot, all global accesses coalesced.
+__global__ void __launch_bounds__(256)
+    merge_tile_start_kernel(const uint64_t *__restrict__ E, long m, long ntiles, uint32_t *__restrict__ tile_u0) {
+  long tile = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tile >= ntiles) return;
+  const uint64_t q0 = (uint64_t)tile * MG_TILE;
+  long lo = 0, hi = m;  // largest u in [0, m] with u + E[u] <= q0
+  while (lo < hi) {
+    long mid = (lo + hi + 1) >> 1;
+    if ((uint64_t)mid + E[mid] <= q0) lo = mid; else hi = mid - 1;
+  }
+  tile_u0[tile] = (uint32_t)lo;
+}
+
 __global__ void __launch_bounds__(SC_THREADS)
-    merge_level_kernel(const uint32_t *__restrict__ sa, const uint64_t *__restrict__ E, long m,
-                       uint64_t beg, const uint32_t *__restrict__ right_lo,
+    merge_level_kernel(const uint32_t *__restrict__ sa, const uint64_t *__restrict__ E,
+                       const uint32_t *__restrict__ tile_u0, long m, uint64_t beg, const uint32_t *__restrict__ right_lo,
                        const uint8_t *__restrict__ right_hi, long total,
                        uint32_t *__restrict__ out_lo, uint8_t *__restrict__ out_hi) {
   constexpr int WORDS = MG_TILE / 32;
   __shared__ uint32_t flags[WORDS];
   __shared__ uint32_t before[WORDS];
-  __shared__ long s_u0;
   const long q0 = (long)blockIdx.x * MG_TILE;
   if (threadIdx.x < WORDS) flags[threadIdx.x] = 0;
-  if (threadIdx.x == 0) {
-    // largest u in [0, m] with u + E[u] <= q0
-    long lo = 0, hi = m;
-    while (lo < hi) {
-      long mid = (lo + hi + 1) >> 1;
-      if ((uint64_t)mid + E[mid] <= (uint64_t)q0) lo = mid; else hi = mid - 1;
-    }
-    s_u0 = lo;
-  }
+  const long u0 = (long)tile_u0[blockIdx.x];
   __syncthreads();
-  const long u0 = s_u0;
   // block suffix u sits at slot u + E[u+1]; only u0 .. u0+MG_TILE-1 can fall into this tile
   for (long e = threadIdx.x; e < MG_TILE; e += SC_THREADS) {
     long u = u0 + e;
@@ -105,8 +109,13 @@ void merge_level(psc_context *ctx, const uint32_t *sa_d, const uint32_t *gap_d, 
   }
   DevBuf<uint64_t> E(ctx, m + 1);
   exclusive_scan_u32_to_u64(ctx, gap_d, E.p, m + 1, nullptr);
-  merge_level_kernel<<<(unsigned)div_up(total, MG_TILE), SC_THREADS, 0, ctx->stream>>>(
-      sa_d, E.p, m, (uint64_t)beg, right_lo, right_hi, total, out_lo, out_hi);
+  const long ntiles = div_up(total, MG_TILE);
+  DevBuf<uint32_t> tile_u0(ctx, ntiles);
+  merge_tile_start_kernel<<<(unsigned)div_up(ntiles, 256), 256, 0, ctx->stream>>>(E.p, m, ntiles, tile_u0.p);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+  merge_level_kernel<<<(unsigned)ntiles, SC_THREADS, 0, ctx->stream>>>(
+      sa_d, E.p, tile_u0.p, m, (uint64_t)beg, right_lo, right_hi, total, out_lo, out_hi);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
 }

@@ -8,31 +8,6 @@ namespace psc {
 constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_TILE = SC_THREADS * SCAN_ITEMS;
 
-__global__ void scan_aggregates_sum_kernel(uint64_t *agg, long n, uint64_t *total_out) {
-  __shared__ uint64_t sm[SC_THREADS / 32 + 1];
-  uint64_t carry = 0;
-  for (long base = 0; base < n; base += SC_THREADS) {
-    long i = base + threadIdx.x;
-    uint64_t v = i < n ? agg[i] : 0, tot;
-    uint64_t ex = block_excl_sum<uint64_t>(v, sm, &tot);
-    if (i < n) agg[i] = carry + ex;
-    carry += tot;
-  }
-  if (threadIdx.x == 0 && total_out) *total_out = carry;
-}
-
-__global__ void scan_aggregates_max_kernel(uint64_t *agg, long n) {
-  __shared__ uint64_t sm[SC_THREADS / 32 + 1];
-  uint64_t carry = 0;
-  for (long base = 0; base < n; base += SC_THREADS) {
-    long i = base + threadIdx.x;
-    uint64_t v = i < n ? agg[i] : 0, tot;
-    uint64_t ex = block_excl_max<uint64_t>(v, sm, &tot);
-    if (i < n) agg[i] = max(carry, ex);
-    carry = max(carry, tot);
-  }
-}
-
 __global__ void __launch_bounds__(SC_THREADS)
     scan_reduce_u32_kernel(const uint32_t *__restrict__ in, long n, uint64_t *__restrict__ agg) {
   __shared__ uint64_t sm[SC_THREADS / 32 + 1];
@@ -63,21 +38,34 @@ __global__ void __launch_bounds__(SC_THREADS)
   }
 }
 
-// one launch for both aggregate arrays of the prefix-doubling grouping: exclusive sum of `asum`
-// (total to *total_out) and exclusive running max of `amax`, 1024 threads per step
-__global__ void __launch_bounds__(1024)
-    scan_aggregates_sum_max_kernel(uint64_t *asum, uint64_t *amax, long n, uint64_t *total_out) {
+// Tile aggregates -> exclusive prefixes, in place, by ONE block: 1024 threads x 8 consecutive
+// aggregates per step (a sum array and/or a running-max array; the prefix-doubling grouping needs
+// both at once).  The tile kernels before and after it carry the real traffic.
+constexpr int AG_THREADS = 1024;
+constexpr int AG_ITEMS = 8;
+
+template <bool SUM, bool MAX>
+__global__ void __launch_bounds__(AG_THREADS)
+    scan_aggregates_kernel(uint64_t *asum, uint64_t *amax, long n, uint64_t *total_out) {
   __shared__ uint64_t ws[32], wm[32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   uint64_t carry_s = 0, carry_m = 0;
-  for (long base = 0; base < n; base += 1024) {
-    long i = base + threadIdx.x;
-    uint64_t vs = i < n ? asum[i] : 0, vm = i < n ? amax[i] : 0;
-    uint64_t is = vs, im = vm;
+  for (long base = 0; base < n; base += AG_THREADS * AG_ITEMS) {
+    const long i0 = base + (long)threadIdx.x * AG_ITEMS;
+    uint64_t vs[AG_ITEMS], vm[AG_ITEMS];
+    uint64_t ts = 0, tm = 0;
+#pragma unroll
+    for (int k = 0; k < AG_ITEMS; ++k) {
+      vs[k] = (SUM && i0 + k < n) ? asum[i0 + k] : 0;
+      vm[k] = (MAX && i0 + k < n) ? amax[i0 + k] : 0;
+      ts += vs[k];
+      tm = max(tm, vm[k]);
+    }
+    uint64_t is = ts, im = tm;  // inclusive over the threads of the warp
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      uint64_t ts = __shfl_up_sync(0xffffffffu, is, o), tm = __shfl_up_sync(0xffffffffu, im, o);
-      if (lane >= o) { is += ts; im = max(im, tm); }
+      uint64_t a = __shfl_up_sync(0xffffffffu, is, o), b = __shfl_up_sync(0xffffffffu, im, o);
+      if (lane >= o) { is += a; im = max(im, b); }
     }
     if (lane == 31) { ws[warp] = is; wm[warp] = im; }
     __syncthreads();
@@ -89,26 +77,35 @@ __global__ void __launch_bounds__(1024)
     }
     uint64_t pm = __shfl_up_sync(0xffffffffu, im, 1);
     if (lane == 0) pm = 0;
-    if (i < n) { asum[i] = carry_s + os + is - vs; amax[i] = max(carry_m, max(om, pm)); }
+    uint64_t ex_s = carry_s + os + is - ts, ex_m = max(carry_m, max(om, pm));
+#pragma unroll
+    for (int k = 0; k < AG_ITEMS; ++k) {
+      if (i0 + k < n) {
+        if (SUM) asum[i0 + k] = ex_s;
+        if (MAX) amax[i0 + k] = ex_m;
+      }
+      ex_s += vs[k];
+      ex_m = max(ex_m, vm[k]);
+    }
     carry_s += tots;
     carry_m = max(carry_m, totm);
     __syncthreads();
   }
-  if (threadIdx.x == 0 && total_out) *total_out = carry_s;
+  if (SUM && threadIdx.x == 0 && total_out) *total_out = carry_s;
 }
+
 void scan_aggregates_sum_max(psc_context *ctx, uint64_t *asum_d, uint64_t *amax_d, long n, uint64_t *total_d) {
-  scan_aggregates_sum_max_kernel<<<1, 1024, 0, ctx->stream>>>(asum_d, amax_d, n, total_d);
+  scan_aggregates_kernel<true, true><<<1, AG_THREADS, 0, ctx->stream>>>(asum_d, amax_d, n, total_d);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
 }
-
 void scan_aggregates_sum(psc_context *ctx, uint64_t *agg_d, long n, uint64_t *total_d) {
-  scan_aggregates_sum_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(agg_d, n, total_d);
+  scan_aggregates_kernel<true, false><<<1, AG_THREADS, 0, ctx->stream>>>(agg_d, nullptr, n, total_d);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
 }
 void scan_aggregates_max(psc_context *ctx, uint64_t *agg_d, long n) {
-  scan_aggregates_max_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(agg_d, n);
+  scan_aggregates_kernel<false, true><<<1, AG_THREADS, 0, ctx->stream>>>(nullptr, agg_d, n, nullptr);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
 }

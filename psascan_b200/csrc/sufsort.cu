@@ -50,12 +50,17 @@ struct RenameLut {
 // ---- round 0 keys --------------------------------------------------------------------------
 // keys[i] = the k renamed symbols at i, packed MSB first; also counts every 8-bit digit of the
 // keys (the radix sort's histogram), so the keys are not read again before the first pass.
+// Each thread builds the keys of PD_ITEMS consecutive positions with a rolling update (one code
+// read per position instead of k); the staged codes are padded by one word per 32 so that the
+// 16-byte thread stride does not collide on shared-memory banks.
+__device__ __forceinline__ int code_slot(int e) { return e + ((e >> 6) << 1); }
+
 __global__ void __launch_bounds__(SC_THREADS)
     init_keys_kernel(const uint8_t *__restrict__ text, long m, const uint32_t *__restrict__ gt_end,
                      RenameLut lut, int passes, uint64_t *__restrict__ keys,
                      unsigned long long *__restrict__ ghist) {
-  extern __shared__ uint16_t codes[];  // PD_TILE + k, then 8 * 256 uint32 histogram
-  uint32_t *sh = reinterpret_cast<uint32_t *>(codes + ((PD_TILE + lut.k + 1) & ~1));
+  extern __shared__ uint16_t codes[];  // code_slot(PD_TILE + k) + 2, then 8 * 256 uint32 histogram
+  uint32_t *sh = reinterpret_cast<uint32_t *>(codes + ((code_slot(PD_TILE + lut.k) + 3) & ~1));
   for (int e = threadIdx.x; e < 8 * 256; e += SC_THREADS) sh[e] = 0;
   const long t0 = (long)blockIdx.x * PD_TILE;
   const int span = PD_TILE + lut.k;
@@ -68,16 +73,33 @@ __global__ void __launch_bounds__(SC_THREADS)
       if (c == lut.last && (i == m - 1 || gt_end == nullptr || bit_get(gt_end, i + 1)))
         cd = lut.code_last_high;
     }
-    codes[e] = cd;
+    codes[code_slot(e)] = cd;
   }
   __syncthreads();
-  for (int e = threadIdx.x; e < PD_TILE; e += SC_THREADS) {
-    long i = t0 + e;
-    if (i >= m) break;
-    uint64_t key = 0;
-    for (int s = 0; s < lut.k; ++s) key = (key << lut.bits) | codes[e + s];
-    keys[i] = key;
-    for (int p = 0; p < passes; ++p) atomicAdd(&sh[p * 256 + (int)((key >> (8 * p)) & 255)], 1u);
+  const int k = lut.k, bits = lut.bits;
+  const uint64_t mask = (k * bits >= 64) ? ~0ull : ((1ull << (k * bits)) - 1ull);
+  const int e0 = threadIdx.x * PD_ITEMS;
+  uint64_t key = 0;
+  for (int j = 0; j < k - 1; ++j) key = (key << bits) | codes[code_slot(e0 + j)];
+  uint64_t out[PD_ITEMS];
+#pragma unroll
+  for (int q = 0; q < PD_ITEMS; ++q) {
+    key = ((key << bits) | codes[code_slot(e0 + k - 1 + q)]) & mask;
+    out[q] = key;
+  }
+  const long i0 = t0 + e0;
+  if (i0 + PD_ITEMS <= m) {
+    ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(keys + i0);
+#pragma unroll
+    for (int q = 0; q < PD_ITEMS; q += 2) dst[q / 2] = make_ulonglong2(out[q], out[q + 1]);
+  } else {
+#pragma unroll
+    for (int q = 0; q < PD_ITEMS; ++q) if (i0 + q < m) keys[i0 + q] = out[q];
+  }
+#pragma unroll
+  for (int q = 0; q < PD_ITEMS; ++q) {
+    if (i0 + q < m)
+      for (int p = 0; p < passes; ++p) atomicAdd(&sh[p * 256 + (int)((out[q] >> (8 * p)) & 255)], 1u);
   }
   __syncthreads();
   for (int e = threadIdx.x; e < passes * 256; e += SC_THREADS)
@@ -303,7 +325,7 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
   long tiles = div_up(m, PD_TILE);
   DevBuf<unsigned long long> ghist(ctx, 8 * 256);
   ghist.zero();
-  init_keys_kernel<<<(unsigned)tiles, SC_THREADS, (PD_TILE + k + 2) * sizeof(uint16_t) + 8 * 256 * 4, ctx->stream>>>(
+  init_keys_kernel<<<(unsigned)tiles, SC_THREADS, (size_t)(PD_TILE + k + (PD_TILE + k) / 32 + 8) * sizeof(uint16_t) + 8 * 256 * 4, ctx->stream>>>(
       text_d, m, gt_end_bits_d, lut, passes, keyA.p, ghist.p);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
