@@ -80,6 +80,15 @@ static void gap_of_block(psc_context *ctx, const uint8_t *block_d, long m, const
   rank_free(rk);
 }
 
+void trace_report(psc_context *ctx) {
+  if (!ctx->trace) return;
+  const psc_stats &st = ctx->stats;
+  fprintf(stderr, "[psc trace] total %.2f ms | sort %.2f (radix passes %.2f) | walk %.2f | merge %.2f | rank %.2f | bwt %.2f | gt_end %.2f\n",
+          st.ms_total, st.ms_sort, st.ms_radix_pass, st.ms_walk, st.ms_merge, st.ms_rank_build, st.ms_bwt, st.ms_gt_end);
+  for (auto &r : ctx->trace_rows) fprintf(stderr, "[psc trace]   %-18s x%-4ld %9.3f ms\n", r.name, r.count, r.ms);
+  ctx->trace_rows.clear();
+}
+
 static void construct_sa_device(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
                                 uint8_t *out_sa5_d) {
   memset(&ctx->stats, 0, sizeof(ctx->stats));
@@ -187,6 +196,7 @@ int psc_init(int device, size_t hbm_budget, psc_context **out) {
     uint64_t thr = UINT64_MAX;
     PSC_CUDA(cudaMemPoolSetAttribute(c->pool, cudaMemPoolAttrReleaseThreshold, &thr));
     c->hbm_budget = hbm_budget;
+    if (const char *e = getenv("PSC_TRACE")) c->trace = atoi(e) != 0;
     memset(&c->stats, 0, sizeof(c->stats));
     *out = c;
   });
@@ -240,6 +250,7 @@ int psc_construct_sa_d(psc_context *ctx, const uint8_t *text_d, long n, long max
     arg_check(ctx && n >= 0 && (n == 0 || (text_d && out_sa5_d)), "psc_construct_sa_d");
     PSC_CUDA(cudaSetDevice(ctx->device));
     construct_sa_device(ctx, text_d, n, max_block, out_sa5_d);
+    trace_report(ctx);
   });
 }
 
@@ -252,6 +263,7 @@ int psc_construct_sa(psc_context *ctx, const uint8_t *text, long n, long max_blo
     double h2d_ms = 0, d2h_ms = 0;
     { PhaseTimer t(ctx, &h2d_ms); h2d(ctx, text_d.p, text, n); }
     construct_sa_device(ctx, text_d.p, n, max_block, out_d.p);
+    trace_report(ctx);
     { PhaseTimer t(ctx, &d2h_ms); d2h(ctx, out_sa5, out_d.p, 5 * (size_t)n); }
     sync(ctx);
     ctx->stats.ms_h2d = h2d_ms;

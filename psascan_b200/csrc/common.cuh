@@ -39,6 +39,10 @@ struct psc_context {
   psc_stats stats;
   long launches = 0;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_free;
+  // PSC_TRACE=1: device time per kernel family, printed to stderr after each construction
+  struct TraceRow { const char *name; long count; double ms; };
+  bool trace = false;
+  std::vector<TraceRow> trace_rows;
 };
 
 namespace psc {
@@ -98,6 +102,30 @@ struct PhaseTimer {
     cudaEventDestroy(a); cudaEventDestroy(b);
   }
 };
+
+// scoped per-kernel timer, active only under PSC_TRACE=1 (it synchronises the stream)
+struct KTrace {
+  psc_context *ctx;
+  const char *name;
+  cudaEvent_t a, b;
+  KTrace(psc_context *c, const char *n) : ctx(c), name(n) {
+    if (!ctx->trace) return;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEventRecord(a, ctx->stream);
+  }
+  ~KTrace() {
+    if (!ctx->trace) return;
+    cudaEventRecord(b, ctx->stream);
+    cudaEventSynchronize(b);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    for (auto &r : ctx->trace_rows)
+      if (r.name == name) { r.count++; r.ms += ms; return; }
+    ctx->trace_rows.push_back({name, 1, (double)ms});
+  }
+};
+void trace_report(psc_context *ctx);
 
 template <typename T>
 static inline void h2d(psc_context *ctx, T *dst, const T *src, size_t n) {

@@ -203,6 +203,7 @@ extern "C" int psc_construct_sa_dist_d(psc_context *ctx, const uint8_t *text_d, 
     }
     PSC_CUDA(cudaSetDevice(ctx->device));
     psc::construct_sa_dist(ctx, text_d, n, max_block, out_sa5_d, rank, world, fn, user);
+    psc::trace_report(ctx);
     return PSC_OK;
   } catch (const psc::CudaError &e) {
     return e.code;

@@ -102,20 +102,20 @@ void merge_level(psc_context *ctx, const uint32_t *sa_d, const uint32_t *gap_d, 
   long total = m + right_len;
   if (total == 0) return;
   if (right_len == 0) {
-    sa_to_planes_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(sa_d, m, (uint64_t)beg, out_lo, out_hi);
+    { KTrace kt(ctx, "sa_to_planes"); sa_to_planes_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(sa_d, m, (uint64_t)beg, out_lo, out_hi); }
     PSC_LAUNCH_CHECK();
     ctx->launches++;
     return;
   }
   DevBuf<uint64_t> E(ctx, m + 1);
-  exclusive_scan_u32_to_u64(ctx, gap_d, E.p, m + 1, nullptr);
+  { KTrace kt(ctx, "gap_scan"); exclusive_scan_u32_to_u64(ctx, gap_d, E.p, m + 1, nullptr); }
   const long ntiles = div_up(total, MG_TILE);
   DevBuf<uint32_t> tile_u0(ctx, ntiles);
-  merge_tile_start_kernel<<<(unsigned)div_up(ntiles, 256), 256, 0, ctx->stream>>>(E.p, m, ntiles, tile_u0.p);
+  { KTrace kt(ctx, "merge_tile_start"); merge_tile_start_kernel<<<(unsigned)div_up(ntiles, 256), 256, 0, ctx->stream>>>(E.p, m, ntiles, tile_u0.p); }
   PSC_LAUNCH_CHECK();
   ctx->launches++;
-  merge_level_kernel<<<(unsigned)ntiles, SC_THREADS, 0, ctx->stream>>>(
-      sa_d, E.p, tile_u0.p, m, (uint64_t)beg, right_lo, right_hi, total, out_lo, out_hi);
+  { KTrace kt(ctx, "merge_level"); merge_level_kernel<<<(unsigned)ntiles, SC_THREADS, 0, ctx->stream>>>(
+      sa_d, E.p, tile_u0.p, m, (uint64_t)beg, right_lo, right_hi, total, out_lo, out_hi); }
   PSC_LAUNCH_CHECK();
   ctx->launches++;
 }
@@ -150,8 +150,8 @@ __global__ void __launch_bounds__(256)
 void pack_sa5(psc_context *ctx, const uint32_t *lo, const uint8_t *hi, long n, uint8_t *out5) {
   PhaseTimer timer(ctx, &ctx->stats.ms_merge);
   if (n <= 0) return;
-  pack_sa5_kernel<<<(unsigned)div_up(div_up(n, 4), 256), 256, 0, ctx->stream>>>(
-      lo, hi, n, reinterpret_cast<uint32_t *>(out5), out5);
+  { KTrace kt(ctx, "pack_sa5"); pack_sa5_kernel<<<(unsigned)div_up(div_up(n, 4), 256), 256, 0, ctx->stream>>>(
+      lo, hi, n, reinterpret_cast<uint32_t *>(out5), out5); }
   PSC_LAUNCH_CHECK();
   ctx->launches++;
 }
@@ -187,8 +187,8 @@ __global__ void __launch_bounds__(256)
 void pack_sa5_from_sa(psc_context *ctx, const uint32_t *sa, long n, long beg, uint8_t *out5) {
   PhaseTimer timer(ctx, &ctx->stats.ms_merge);
   if (n <= 0) return;
-  pack_sa32_kernel<<<(unsigned)div_up(div_up(n, 4), 256), 256, 0, ctx->stream>>>(
-      sa, n, (uint64_t)beg, reinterpret_cast<uint32_t *>(out5), out5);
+  { KTrace kt(ctx, "pack_sa32"); pack_sa32_kernel<<<(unsigned)div_up(div_up(n, 4), 256), 256, 0, ctx->stream>>>(
+      sa, n, (uint64_t)beg, reinterpret_cast<uint32_t *>(out5), out5); }
   PSC_LAUNCH_CHECK();
   ctx->launches++;
 }

@@ -62,16 +62,29 @@ struct PassCfg {
 
 // lanes of the warp holding the same digit.  USE_MATCH: match.any (one ADU instruction, measured
 // ~60 cycles of the SM's ADU pipe per warp) else eight ballots (ALU/vote pipes; 1.55x faster per pass).
+// The ballot form is written in PTX: four instructions per digit bit (test, vote, select, and-xnor);
+// the compiler's own translation of the C++ took seven.
 template <bool USE_MATCH>
 __device__ __forceinline__ uint32_t digit_peers(int d) {
   if (USE_MATCH) return __match_any_sync(0xffffffffu, d);
-  uint32_t peers = 0xffffffffu;
-#pragma unroll
-  for (int b = 0; b < 8; ++b) {
-    bool bit = (d >> b) & 1;
-    uint32_t bal = __ballot_sync(0xffffffffu, bit);
-    peers &= bal ^ (bit ? 0u : 0xffffffffu);
-  }
+  uint32_t peers;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .b32 t, bal, m;\n\t"
+      "mov.b32 %0, 0xffffffff;\n\t"
+#define PSC_PEER_BIT(B)                                        \
+      "and.b32 t, %1, " #B ";\n\t"                             \
+      "setp.ne.u32 p, t, 0;\n\t"                               \
+      "vote.sync.ballot.b32 bal, p, 0xffffffff;\n\t"           \
+      "selp.b32 m, 0xffffffff, 0, p;\n\t"                      \
+      "lop3.b32 %0, %0, bal, m, 0x90;\n\t" /* a & ~(b ^ c) */
+      PSC_PEER_BIT(1) PSC_PEER_BIT(2) PSC_PEER_BIT(4) PSC_PEER_BIT(8)
+      PSC_PEER_BIT(16) PSC_PEER_BIT(32) PSC_PEER_BIT(64) PSC_PEER_BIT(128)
+#undef PSC_PEER_BIT
+      "}"
+      : "=r"(peers)
+      : "r"(d));
   return peers;
 }
 
@@ -86,7 +99,8 @@ __global__ void __launch_bounds__(THREADS, MINB)
                       uint64_t *__restrict__ kout, uint32_t *__restrict__ vout, long n, int shift,
                       const uint64_t *__restrict__ gscan,  // [256] exclusive global digit offsets
                       uint64_t *status,                    // [tiles][256] look-back chain
-                      uint32_t *tile_counter) {
+                      uint32_t *tile_counter,
+                      int pf_dist) {  // > 0: pull the tile `pf_dist` ahead into L2 (bulk prefetch)
   constexpr int WARPS = THREADS / 32;
   constexpr int TILE = THREADS * ITEMS;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -104,6 +118,17 @@ __global__ void __launch_bounds__(THREADS, MINB)
   const long tile = wsum[8];
   const long tile_beg = tile * TILE;
   const int valid = (int)min((long)TILE, n - tile_beg);
+  if (pf_dist > 0 && tid == THREADS - 32) {
+    // tiles are handed out in order, so tile + (number of resident CTAs) is what this SM slot
+    // will most likely load next: have the copy engine fetch it into L2 while this tile is processed
+    const long pb = (tile + pf_dist) * TILE;
+    if (pb < n) {
+      const long cnt = min((long)TILE, n - pb);
+      const uint32_t kb = (uint32_t)((cnt * 8) & ~15L), vb = (uint32_t)((cnt * 4) & ~15L);
+      if (kb) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(kin + pb), "r"(kb) : "memory");
+      if (vin && vb) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(vin + pb), "r"(vb) : "memory");
+    }
+  }
 
   // load: element order inside the tile is (warp, item, lane)
   uint64_t key[ITEMS];
@@ -208,10 +233,10 @@ __global__ void __launch_bounds__(THREADS, MINB)
 }
 
 typedef void (*PassFn)(const uint64_t *, const uint32_t *, uint64_t *, uint32_t *, long, int, const uint64_t *,
-                       uint64_t *, uint32_t *);
-struct PassVariant { const char *name; PassFn fn; int threads, tile; size_t smem; };
+                       uint64_t *, uint32_t *, int);
+struct PassVariant { const char *name; PassFn fn; int threads, tile; size_t smem; int minb; };
 #define PASS_VARIANT(T, I, B, M) \
-  { #T "x" #I "b" #B "m" #M, radix_pass_kernel<T, I, B, M>, T, PassCfg<T, I>::TILE, PassCfg<T, I>::SMEM }
+  { #T "x" #I "b" #B "m" #M, radix_pass_kernel<T, I, B, M>, T, PassCfg<T, I>::TILE, PassCfg<T, I>::SMEM, B }
 // first entry = default (measured best on B200: 2.17 ms per pass of 2^28 pairs = 2.97 TB/s);
 // PSC_RADIX_VARIANT selects another one for tuning runs (tools/tune_radix.py)
 static const PassVariant g_variants[] = {
@@ -285,6 +310,9 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
 
   const PassVariant &pv = pass_variant();
   long tiles = div_up(n, pv.tile);
+  static int pf_mult = -1;  // prefetch distance in units of resident CTAs (PSC_RADIX_PF, 0 = off)
+  if (pf_mult < 0) { const char *e = getenv("PSC_RADIX_PF"); pf_mult = e ? atoi(e) : 1; }
+  const int pf_dist = pf_mult * ctx->n_sm * pv.minb;
   DevBuf<uint64_t> status(ctx, (size_t)tiles * RADIX);
   DevBuf<uint32_t> counter(ctx, 1);
   uint64_t *kin = keys_a, *kout = keys_b;
@@ -298,7 +326,7 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     cudaEventRecord(e0, ctx->stream);
     pv.fn<<<(unsigned)tiles, pv.threads, pv.smem, ctx->stream>>>(
-        kin, vals_iota ? nullptr : vin, kout, vout, n, sl.s[p], gscan.p + p * RADIX, status.p, counter.p);
+        kin, vals_iota ? nullptr : vin, kout, vout, n, sl.s[p], gscan.p + p * RADIX, status.p, counter.p, pf_dist);
     vals_iota = false;
     cudaEventRecord(e1, ctx->stream);
     evs.push_back({e0, e1});

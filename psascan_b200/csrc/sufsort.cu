@@ -282,7 +282,7 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
   DevBuf<unsigned long long> hist_d(ctx, 257);
   hist_d.zero();
   int hb = (int)std::min<long>(div_up(m, 256 * 16), (long)ctx->n_sm * 8);
-  symbol_hist_kernel<<<hb, 256, 0, ctx->stream>>>(text_d, m, gt_end_bits_d, last, hist_d.p);
+  { KTrace kt(ctx, "symbol_hist"); symbol_hist_kernel<<<hb, 256, 0, ctx->stream>>>(text_d, m, gt_end_bits_d, last, hist_d.p); }
   PSC_LAUNCH_CHECK();
   ctx->launches++;
   unsigned long long hist[257];
@@ -325,8 +325,8 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
   long tiles = div_up(m, PD_TILE);
   DevBuf<unsigned long long> ghist(ctx, 8 * 256);
   ghist.zero();
-  init_keys_kernel<<<(unsigned)tiles, SC_THREADS, (size_t)(PD_TILE + k + (PD_TILE + k) / 32 + 8) * sizeof(uint16_t) + 8 * 256 * 4, ctx->stream>>>(
-      text_d, m, gt_end_bits_d, lut, passes, keyA.p, ghist.p);
+  { KTrace kt(ctx, "init_keys"); init_keys_kernel<<<(unsigned)tiles, SC_THREADS, (size_t)(PD_TILE + k + (PD_TILE + k) / 32 + 8) * sizeof(uint16_t) + 8 * 256 * 4, ctx->stream>>>(
+      text_d, m, gt_end_bits_d, lut, passes, keyA.p, ghist.p); }
   PSC_LAUNCH_CHECK();
   ctx->launches++;
   DevBuf<uint64_t> key_of_zero(ctx, 1), total_d(ctx, 1);
@@ -337,7 +337,7 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
   for (int p = 0; p < passes; ++p) shifts[p] = 8 * p;
   uint64_t *K; uint32_t *V;
   radix_sort_pairs(ctx, keyA.p, valA.p, keyB.p, valB.p, m, shifts, passes, &K, &V, ghist.p, true);
-  find_i0_kernel<<<(unsigned)div_up(m, 4096), 256, 0, ctx->stream>>>(K, V, m, key_of_zero.p, i0_d.p);
+  { KTrace kt(ctx, "find_i0"); find_i0_kernel<<<(unsigned)div_up(m, 4096), 256, 0, ctx->stream>>>(K, V, m, key_of_zero.p, i0_d.p); }
   PSC_LAUNCH_CHECK();
   ctx->launches++;
 
@@ -358,9 +358,9 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
   for (int round = 0;; ++round) {
     long t = div_up(a, PD_TILE);
     DevBuf<uint64_t> agg_act(ctx, t), agg_head(ctx, t);
-    group_reduce_kernel<<<(unsigned)t, SC_THREADS, 0, ctx->stream>>>(K, a, agg_act.p, agg_head.p);
+    { KTrace kt(ctx, "group_reduce"); group_reduce_kernel<<<(unsigned)t, SC_THREADS, 0, ctx->stream>>>(K, a, agg_act.p, agg_head.p); }
     PSC_LAUNCH_CHECK();
-    scan_aggregates_sum_max(ctx, agg_act.p, agg_head.p, t, total_d.p);
+    { KTrace kt(ctx, "scan_aggregates"); scan_aggregates_sum_max(ctx, agg_act.p, agg_head.p, t, total_d.p); }
     uint64_t na = 0;
     d2h(ctx, &na, total_d.p, 1);
     sync(ctx);
@@ -369,9 +369,9 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
       vbuf[1] = valC.p;
     }
     posbuf[pout].alloc(ctx, na);
-    group_apply_kernel<<<(unsigned)t, SC_THREADS, 0, ctx->stream>>>(
+    { KTrace kt(ctx, "group_apply"); group_apply_kernel<<<(unsigned)t, SC_THREADS, 0, ctx->stream>>>(
         K, V, pos, a, agg_act.p, agg_head.p, round == 0 ? nullptr : res->sa.p, res->isa.p, kbuf[out], vbuf[out],
-        posbuf[pout].p, i0_d.p);
+        posbuf[pout].p, i0_d.p); }
     PSC_LAUNCH_CHECK();
     ctx->launches += 2;
     ctx->stats.doubling_rounds++;
@@ -386,8 +386,8 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
     if (!text_round_done && k1 >= 1) {
       // text round: extend the compared prefix by k1 symbols read from the text (no ISA yet)
       text_round_done = true;
-      second_key_text_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, text_d, m, gt_end_bits_d,
-                                                                                lut, h, k1);
+      { KTrace kt(ctx, "second_key_text"); second_key_text_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, text_d, m, gt_end_bits_d,
+                                                                                lut, h, k1); }
       PSC_LAUNCH_CHECK();
       for (int b = 0; b < k1 * lut.bits + hpbits; b += 8) shifts[nsh++] = b;
       h += k1;
@@ -396,13 +396,13 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
       if (res->isa.p == nullptr) {
         // first doubling round: now the full inverse suffix array is needed
         res->isa.alloc(ctx, m);
-        isa_scatter_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(res->sa.p, m, res->isa.p);
+        { KTrace kt(ctx, "isa_scatter"); isa_scatter_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(res->sa.p, m, res->isa.p); }
         PSC_LAUNCH_CHECK();
-        isa_fix_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, res->isa.p);
+        { KTrace kt(ctx, "isa_fix"); isa_fix_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, res->isa.p); }
         PSC_LAUNCH_CHECK();
         ctx->launches += 2;
       }
-      second_key_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, res->isa.p, m, h);
+      { KTrace kt(ctx, "second_key"); second_key_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, res->isa.p, m, h); }
       PSC_LAUNCH_CHECK();
       for (int b = 0; b < lowb; b += 8) shifts[nsh++] = b;
       for (int b = 0; b < hpbits; b += 8) shifts[nsh++] = 32 + b;

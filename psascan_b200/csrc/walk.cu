@@ -243,9 +243,9 @@ void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, con
     DevBuf<uint32_t> emit(ctx, T), part(ctx, T);
     DevBuf<unsigned long long> bc(ctx, WK_MAX_BUCKETS), cur(ctx, WK_MAX_BUCKETS);
     bc.zero();
-    lf_walk_kernel<2><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d, start_rank_d,
+    { KTrace kt(ctx, "lf_walk(emit)"); lf_walk_kernel<2><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d, start_rank_d,
                                                         gt_in_bits_d, gt_in_off, gt_out_bits_d, gt_out_off, gap_d,
-                                                        emit.p, lo, bshift, nb, bc.p);
+                                                        emit.p, lo, bshift, nb, bc.p); }
     PSC_LAUNCH_CHECK();
     unsigned long long h[WK_MAX_BUCKETS], c[WK_MAX_BUCKETS];
     d2h(ctx, h, bc.p, nb);
@@ -253,10 +253,10 @@ void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, con
     unsigned long long run = 0;
     for (int b = 0; b < nb; ++b) { c[b] = run; run += h[b]; }
     h2d(ctx, cur.p, c, nb);
-    rank_partition_kernel<<<(unsigned)div_up(T, PT_TILE), PT_THREADS, 0, ctx->stream>>>(emit.p, T, bshift, nb, cur.p,
-                                                                                      part.p);
+    { KTrace kt(ctx, "rank_partition"); rank_partition_kernel<<<(unsigned)div_up(T, PT_TILE), PT_THREADS, 0, ctx->stream>>>(emit.p, T, bshift, nb, cur.p,
+                                                                                      part.p); }
     PSC_LAUNCH_CHECK();
-    rank_accumulate_kernel<<<(unsigned)div_up(div_up(T, 4), 256), 256, 0, ctx->stream>>>(part.p, T, gap_d);
+    { KTrace kt(ctx, "rank_accumulate"); rank_accumulate_kernel<<<(unsigned)div_up(div_up(T, 4), 256), 256, 0, ctx->stream>>>(part.p, T, gap_d); }
     PSC_LAUNCH_CHECK();
     sync(ctx);
     ctx->launches += 3;
@@ -266,9 +266,9 @@ void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, con
                                                           gt_in_bits_d, gt_in_off, gt_out_bits_d, gt_out_off, gap_d,
                                                           nullptr, 0, 0, 0, nullptr);
     else
-      lf_walk_kernel<0><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d, start_rank_d,
+      { KTrace kt(ctx, "lf_walk(red)"); lf_walk_kernel<0><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d, start_rank_d,
                                                           gt_in_bits_d, gt_in_off, gt_out_bits_d, gt_out_off, gap_d,
-                                                          nullptr, 0, 0, 0, nullptr);
+                                                          nullptr, 0, 0, 0, nullptr); }
     PSC_LAUNCH_CHECK();
     sync(ctx);  // tb is a stack object
     ctx->launches++;
