@@ -37,18 +37,6 @@ __global__ void or_not_bit_kernel(const uint32_t *src_bits, long src_idx, int sr
   if (!s) atomicOr(&dst_bits[dst_idx >> 5], 1u << (dst_idx & 31));
 }
 
-// walker layout for a tail of t symbols: equal slices, boundaries on multiples of 32
-static void plan_walkers(psc_context *ctx, long t, std::vector<uint64_t> *beg) {
-  long target = (long)ctx->n_sm * 2048;
-  if (const char *e = getenv("PSC_WALKERS")) target = std::max(1L, atol(e));
-  long slice = div_up(t, target);
-  slice = std::max(64L, div_up(slice, 32) * 32);
-  long W = div_up(t, slice);
-  beg->resize(W + 1);
-  for (long k = 0; k < W; ++k) (*beg)[k] = (uint64_t)(k * slice);
-  (*beg)[W] = (uint64_t)t;
-}
-
 // Stages 2+3 for one block against the text after it (all device pointers).
 //   gt_cur: bits relative to the block end, bit index = global position - 1 - bit_base
 static void gap_of_block(psc_context *ctx, const uint8_t *block_d, long m, const uint32_t *sa_d,
@@ -63,21 +51,63 @@ static void gap_of_block(psc_context *ctx, const uint8_t *block_d, long m, const
   try {
     uint64_t Cmap[256], run = 0;
     for (int c = 0; c < 256; ++c) { Cmap[c] = run; run += (uint64_t)rk->counts[c] + (c == last ? 1 : 0); }
-    std::vector<uint64_t> wb;
-    plan_walkers(ctx, t, &wb);
-    long W = (long)wb.size() - 1;
-    DevBuf<uint64_t> wb_d(ctx, W + 1), sr_d(ctx, W);
-    h2d(ctx, wb_d.p, wb.data(), wb.size());
-    // walker k starts from the rank of suffix(after + wb[k+1]); the last one from suffix(n): 0
-    initial_ranks(ctx, block_d, sa_d, m, after_d, t, 1, gt_cur, gt_off, W, wb_d.p + 1, sr_d.p);
-    lf_walk(ctx, rk, (uint32_t)i0, last, Cmap, after_d, t, 0, W, wb_d.p, sr_d.p, gt_cur, gt_off, gt_new,
-            gt_off, gap_d);
-    sync(ctx);
+    walk_tail_range(ctx, rk, i0, last, Cmap, block_d, sa_d, m, after_d, t, 0, t, gt_cur, gt_off, gt_new, gap_d);
   } catch (...) {
     rank_free(rk);
     throw;
   }
   rank_free(rk);
+}
+
+// ---- buffer cache ------------------------------------------------------------------------------
+static size_t size_class(size_t bytes) {
+  // 16 classes per octave (<= 6.25 % slack), at least 512-byte steps
+  if (bytes < 8192) return (bytes + 511) & ~(size_t)511;
+  int lg = 63 - __builtin_clzll((unsigned long long)bytes);
+  size_t step = (size_t)1 << (lg - 4);
+  return (bytes + step - 1) & ~(step - 1);
+}
+
+void cache_trim(psc_context *ctx) {
+  size_t k = 0;
+  for (auto &b : ctx->cache) {
+    if (b.used) ctx->cache[k++] = b;
+    else cudaFreeAsync(b.p, ctx->stream);
+  }
+  ctx->cache.resize(k);
+  ctx->cache_free_bytes = 0;
+}
+
+void *cache_alloc(psc_context *ctx, size_t bytes) {
+  const size_t cls = size_class(bytes);
+  for (auto &b : ctx->cache)
+    if (!b.used && b.bytes == cls) { b.used = true; ctx->cache_free_bytes -= cls; return b.p; }
+  void *q = nullptr;
+  auto t0 = std::chrono::steady_clock::now();
+  cudaError_t e = cudaMallocAsync(&q, cls, ctx->stream);
+  if (e == cudaErrorMemoryAllocation && ctx->cache_free_bytes) {  // unused classes hold the memory
+    cudaGetLastError();
+    cache_trim(ctx);
+    cudaStreamSynchronize(ctx->stream);
+    e = cudaMallocAsync(&q, cls, ctx->stream);
+  }
+  if (ctx->trace) {
+    ctx->host_alloc_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    ctx->n_allocs++;
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    set_error("device allocation of %zu bytes failed: %s", cls, cudaGetErrorString(e));
+    throw CudaError{e == cudaErrorMemoryAllocation ? PSC_ENOMEM : PSC_ECUDA};
+  }
+  ctx->cache.push_back({q, cls, true});
+  return q;
+}
+
+void cache_release(psc_context *ctx, void *p) {
+  for (auto &b : ctx->cache)
+    if (b.p == p) { b.used = false; ctx->cache_free_bytes += b.bytes; return; }
+  cudaFreeAsync(p, ctx->stream);  // not ours (cannot happen)
 }
 
 void trace_report(psc_context *ctx) {
@@ -86,6 +116,10 @@ void trace_report(psc_context *ctx) {
   fprintf(stderr, "[psc trace] total %.2f ms | sort %.2f (radix passes %.2f) | walk %.2f | merge %.2f | rank %.2f | bwt %.2f | gt_end %.2f\n",
           st.ms_total, st.ms_sort, st.ms_radix_pass, st.ms_walk, st.ms_merge, st.ms_rank_build, st.ms_bwt, st.ms_gt_end);
   for (auto &r : ctx->trace_rows) fprintf(stderr, "[psc trace]   %-18s x%-4ld %9.3f ms\n", r.name, r.count, r.ms);
+  fprintf(stderr, "[psc trace]   host time in %ld cudaMallocAsync calls: %.3f ms; %zu cached buffers, %.1f MB unused\n", ctx->n_allocs,
+          ctx->host_alloc_ms, ctx->cache.size(), ctx->cache_free_bytes / 1e6);
+  ctx->host_alloc_ms = 0;
+  ctx->n_allocs = 0;
   ctx->trace_rows.clear();
 }
 
@@ -205,6 +239,7 @@ int psc_init(int device, size_t hbm_budget, psc_context **out) {
 int psc_shutdown(psc_context *ctx) {
   if (!ctx) return PSC_OK;
   cudaSetDevice(ctx->device);
+  cache_trim(ctx);
   cudaStreamSynchronize(ctx->stream);
   cudaMemPoolTrimTo(ctx->pool, 0);
   cudaStreamDestroy(ctx->stream);
@@ -217,6 +252,8 @@ long psc_max_block_size(psc_context *ctx, long n) {
   if (!ctx || n <= 0) return 0;
   size_t free_b = 0, total_b = 0;
   cudaSetDevice(ctx->device);
+  cache_trim(ctx);
+  cudaStreamSynchronize(ctx->stream);
   if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 0;
   uint64_t reserved = 0;
   cudaMemPoolGetAttribute(ctx->pool, cudaMemPoolAttrReservedMemCurrent, &reserved);

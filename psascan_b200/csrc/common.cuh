@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <string>
+#include <chrono>
 #include <vector>
 #include "../../include/psascan_cuda.h"
 
@@ -43,9 +44,23 @@ struct psc_context {
   struct TraceRow { const char *name; long count; double ms; };
   bool trace = false;
   std::vector<TraceRow> trace_rows;
+  double host_alloc_ms = 0;  // host time inside cudaMallocAsync / cudaFreeAsync (trace only)
+  long n_allocs = 0;
+  // Device buffers released by the pipeline are kept here and handed out again by size class:
+  // the driver's pool took 0.2-1 ms of host time per call once block sizes started to vary
+  // (measured 76-390 ms per 1 GiB / 8 block construction), all work is on one stream so reuse
+  // needs no synchronisation.
+  struct CacheBlock { void *p; size_t bytes; bool used; };
+  std::vector<CacheBlock> cache;
+  size_t cache_free_bytes = 0;
 };
 
 namespace psc {
+
+// api.cu: size-class cache in front of cudaMallocAsync (throws CudaError on failure)
+void *cache_alloc(psc_context *ctx, size_t bytes);
+void cache_release(psc_context *ctx, void *p);
+void cache_trim(psc_context *ctx);  // give every unused cached buffer back to the pool
 
 // Stream-ordered device buffer (cudaMallocAsync pool: freed blocks are reused without
 // going back to the driver).
@@ -68,18 +83,11 @@ struct DevBuf {
     ctx = c;
     n = count;
     size_t bytes = (count ? count : 1) * sizeof(T) + 256;  // slack: kernels may read whole vectors
-    void *q = nullptr;
-    cudaError_t e = cudaMallocAsync(&q, bytes, c->stream);
-    if (e != cudaSuccess) {
-      cudaGetLastError();
-      set_error("device allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
-      throw CudaError{e == cudaErrorMemoryAllocation ? PSC_ENOMEM : PSC_ECUDA};
-    }
-    p = (T *)q;
+    p = (T *)cache_alloc(c, bytes);
   }
   void zero() { PSC_CUDA(cudaMemsetAsync(p, 0, (n ? n : 1) * sizeof(T) + 256, ctx->stream)); }
   void release() {
-    if (p) { cudaFreeAsync(p, ctx->stream); p = nullptr; n = 0; }
+    if (p) { cache_release(ctx, p); p = nullptr; n = 0; }
   }
   ~DevBuf() { release(); }
   operator T *() const { return p; }
@@ -249,6 +257,11 @@ void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, con
              const uint8_t *tail_d, long t, long lo, long nwalk, const uint64_t *walk_beg_d,
              const uint64_t *start_rank_d, const uint32_t *gt_in_bits_d, long gt_in_off,
              uint32_t *gt_out_bits_d, long gt_out_off, uint32_t *gap_d);
+
+// K5 + K6 over tail positions [lo, hi), chunked (walk.cu)
+void walk_tail_range(psc_context *ctx, const psc_rank *rk, long i0, uint8_t last, const uint64_t *Cmap,
+                     const uint8_t *block_d, const uint32_t *sa_d, long m, const uint8_t *after_d, long t,
+                     long lo, long hi, const uint32_t *gt_cur, long gt_off, uint32_t *gt_new, uint32_t *gap_d);
 
 // merge.cu: planes lo32/hi8 for the running merged SA.
 void merge_level(psc_context *ctx, const uint32_t *sa_d, const uint32_t *gap_d, long m, long beg,

@@ -146,19 +146,9 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
         // my contiguous share of the tail, boundaries on multiples of 32
         long per = div_up(div_up(t, (long)world), 32) * 32;
         long lo = std::min(t, per * rank), hi = std::min(t, per * (rank + 1));
-        if (hi > lo) {
-          long target = std::max(1L, (long)ctx->n_sm * 2048);
-          long slice = std::max(64L, div_up(div_up(hi - lo, target), 32) * 32);
-          long W = div_up(hi - lo, slice);
-          std::vector<uint64_t> wb(W + 1);
-          for (long k = 0; k < W; ++k) wb[k] = (uint64_t)(lo + k * slice);
-          wb[W] = (uint64_t)hi;
-          DevBuf<uint64_t> wb_d(ctx, W + 1), sr_d(ctx, W);
-          h2d(ctx, wb_d.p, wb.data(), wb.size());
-          initial_ranks(ctx, text_d + beg, sa_p, m, text_d + end, t, 1, gt_cur, end, W, wb_d.p + 1, sr_d.p);
-          lf_walk(ctx, rk, (uint32_t)i0, (uint8_t)meta.last, Cmap, text_d + end, hi - lo, lo, W, wb_d.p, sr_d.p, gt_cur,
-                  end, id > 0 ? gt_new : nullptr, end, gap.p);
-        }
+        if (hi > lo)
+          walk_tail_range(ctx, rk, i0, (uint8_t)meta.last, Cmap, text_d + beg, sa_p, m, text_d + end, t, lo, hi, gt_cur,
+                          end, id > 0 ? gt_new : nullptr, gap.p);
       } catch (...) { rank_free(rk); throw; }
       rank_free(rk);
       if (world > 1) {

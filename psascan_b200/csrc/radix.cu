@@ -205,14 +205,26 @@ __global__ void __launch_bounds__(THREADS, MINB)
   if (tid < RADIX) {
     uint64_t excl = 0;
     if (tile > 0) {
+      // predecessors are read LB at a time (independent loads, one L2 round trip): measured
+      // depth of the walk was 14 tiles = 14 dependent round trips with one load per step
+      constexpr int LB = 8;
       long t = tile - 1;
-      while (true) {
-        uint64_t v = ld_relaxed_u64(status + (size_t)t * RADIX + tid);
-        uint64_t f = v & ~ST_MASK;
-        if (f == 0) continue;
-        excl += v & ST_MASK;
-        if (f == ST_INCL) break;
-        --t;
+      bool done = false;
+      while (!done) {
+        uint64_t v[LB];
+#pragma unroll
+        for (int j = 0; j < LB; ++j) v[j] = (t - j >= 0) ? ld_relaxed_u64(status + (size_t)(t - j) * RADIX + tid) : ST_INCL;
+        int used = 0;
+#pragma unroll
+        for (int j = 0; j < LB; ++j) {
+          uint64_t f = v[j] & ~ST_MASK;
+          if (!done && used == j && f != 0) {
+            excl += v[j] & ST_MASK;
+            used = j + 1;
+            if (f == ST_INCL) done = true;
+          }
+        }
+        t -= used;  // an unpublished status stops the batch; it is read again
       }
       uint32_t cnt_valid = cnt - ((tid == 255) ? (uint32_t)(TILE - valid) : 0u);
       st_relaxed_u64(status + (size_t)tile * RADIX + tid, ST_INCL | (excl + cnt_valid));

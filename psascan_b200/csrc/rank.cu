@@ -129,15 +129,9 @@ psc_rank *rank_build(psc_context *ctx, const uint8_t *bwt_d, long m, long i0) {
   }
   r->n_codes = nc;
   size_t bytes = (size_t)std::max(nc, 1) * (size_t)r->n_sectors * 32 + 256;
-  void *q = nullptr;
-  cudaError_t e = cudaMallocAsync(&q, bytes, ctx->stream);
-  if (e != cudaSuccess) {
-    cudaGetLastError();
-    delete r;
-    set_error("rank structure allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
-    throw CudaError{PSC_ENOMEM};
-  }
-  r->sectors_d = (uint32_t *)q;
+  try {
+    r->sectors_d = (uint32_t *)cache_alloc(ctx, bytes);
+  } catch (...) { delete r; throw; }
   if (nc > 0) {
     DevBuf<uint8_t> soc(ctx, 256);
     h2d(ctx, soc.p, sym_of_code, 256);
@@ -153,7 +147,7 @@ psc_rank *rank_build(psc_context *ctx, const uint8_t *bwt_d, long m, long i0) {
 
 void rank_free(psc_rank *r) {
   if (!r) return;
-  if (r->sectors_d) cudaFreeAsync(r->sectors_d, r->ctx->stream);
+  if (r->sectors_d) cache_release(r->ctx, r->sectors_d);
   delete r;
 }
 

@@ -9,6 +9,8 @@
 // compute_gap.hpp:77-85): one walker per thread, thousands per SM, each doing the dependent
 // chain i <- C[c] + occ(c, i) (+1) with one 32-byte sector read per step and a RED on the
 // uint32 gap counter (optionally warp-aggregated through match.any).
+#include <algorithm>
+#include <vector>
 #include "rank.cuh"
 
 namespace psc {
@@ -275,6 +277,39 @@ void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, con
   }
   ctx->stats.lf_steps += t;
   ctx->stats.walkers = nwalk;
+}
+
+// Stages 2+3 for tail positions [lo, hi) of the text after a block: in chunks of at most
+// PSC_WALK_CHUNK positions (2^29: 4 GB of rank-stream scratch whatever the tail length), each chunk
+// cut into equal walker slices with boundaries on multiples of 32 (compute_gap.hpp:68-69 cuts the
+// tail over threads the same way), initial ranks by binary search, then the walk.
+void walk_tail_range(psc_context *ctx, const psc_rank *rk, long i0, uint8_t last, const uint64_t *Cmap,
+                     const uint8_t *block_d, const uint32_t *sa_d, long m, const uint8_t *after_d, long t,
+                     long lo, long hi, const uint32_t *gt_cur, long gt_off, uint32_t *gt_new, uint32_t *gap_d) {
+  static long chunk = 0, target_env = -1;
+  if (!chunk) {
+    const char *e = getenv("PSC_WALK_CHUNK");
+    chunk = e ? std::max(64L, atol(e) / 32 * 32) : (1L << 29);
+    const char *w = getenv("PSC_WALKERS");
+    target_env = w ? std::max(1L, atol(w)) : 0;
+  }
+  const long target = target_env > 0 ? target_env : (long)ctx->n_sm * 2048;
+  std::vector<uint64_t> wb;
+  for (long clo = lo; clo < hi; clo += chunk) {
+    const long chi = std::min(hi, clo + chunk);
+    long slice = std::max(64L, div_up(div_up(chi - clo, target), 32) * 32);
+    const long W = div_up(chi - clo, slice);
+    wb.resize(W + 1);
+    for (long k = 0; k < W; ++k) wb[k] = (uint64_t)(clo + k * slice);
+    wb[W] = (uint64_t)chi;
+    DevBuf<uint64_t> wb_d(ctx, W + 1), sr_d(ctx, W);
+    h2d(ctx, wb_d.p, wb.data(), wb.size());
+    // walker k starts from the rank of suffix(after + wb[k+1]); the one ending at t from suffix(n): 0
+    initial_ranks(ctx, block_d, sa_d, m, after_d, t, 1, gt_cur, gt_off, W, wb_d.p + 1, sr_d.p);
+    lf_walk(ctx, rk, (uint32_t)i0, last, Cmap, after_d, chi - clo, clo, W, wb_d.p, sr_d.p, gt_cur, gt_off, gt_new,
+            gt_off, gap_d);
+    sync(ctx);  // wb is reused by the next chunk
+  }
 }
 
 }  // namespace psc
