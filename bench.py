@@ -270,6 +270,18 @@ def main():
                     "launches_per_step": s["radix_passes"],
                     "avg_launch_ms": s["ms_radix_pass"] / max(1, s["radix_passes"]),
                     "peak": peak, "peak_source": peak_src, "traffic": None}
+        # DRAM bytes of one launch from the committed ncu --set full capture (profiles/), scaled to
+        # the units of an average launch of this run
+        try:
+            tr = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")))
+            k = tr[roof["kernel"]]
+            units = (s["lf_steps"] / max(1, s["n_blocks"] - 1)) if roof["kernel"] == "lf_walk_kernel" \
+                else s["radix_elems"] / max(1, s["radix_passes"])
+            roof["traffic"] = k["dram_bytes"] / k["units"] * units
+            roof["traffic_source"] = k["source"]
+            roof["algorithmic_bytes_per_launch"] = roof["algorithmic_bytes_per_unit"] * units
+        except Exception:
+            roof["traffic"] = None
         if roof["achieved"]:
             roof["frac"] = roof["achieved"] / peak
         line = {"metric": "SA construction input MB/s", "value": value, "unit": "MB/s", "n_gpus": world,

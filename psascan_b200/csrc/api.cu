@@ -267,7 +267,8 @@ long psc_max_block_size(psc_context *ctx, long n) {
   // multi block: text n + merged planes 10n + output 5n + gt bits; per block symbol: 40 B sort state,
   // or sa + gap + bwt + rank planes (<= 255 * 32/224 B) while streaming
   double per_block = 48.0;
-  double rest = avail - 16.3 * (double)n;
+  // + the rank stream of one walk chunk (2 x 4 B x 2^29 positions at most, walk.cu)
+  double rest = avail - 16.3 * (double)n - 8.0 * (double)std::min(n, 1L << 29);
   if (rest <= 0) return 0;
   long mb = (long)(rest / per_block);
   mb = std::min(mb, (1L << 31) - 4096);

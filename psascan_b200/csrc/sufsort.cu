@@ -237,6 +237,89 @@ __global__ void __launch_bounds__(256)
   long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < m) isa[sa[i]] = (uint32_t)i;
 }
+// The same scatter for blocks whose ISA does not fit in L2 (measured: the direct scatter moves a
+// 32-byte sector in and out of HBM per element, 5.1 ms for 2^27 elements): the pairs (sa[i], i) are
+// first grouped by ISA range of 2^22 entries (16 MB), then scattered range after range with the
+// target lines resident in L2.  The SA is a permutation, so range b receives exactly 2^22 pairs and
+// its slots in the pair array are known without a counting pass.
+constexpr int IP_THREADS = 512;
+constexpr int IP_ITEMS = 8;
+constexpr int IP_TILE = IP_THREADS * IP_ITEMS;  // 4096 pairs, 32 KB of staging
+constexpr int IP_SHIFT = 22;
+constexpr int IP_MAX_BUCKETS = 512;  // m < 2^31
+
+__global__ void isa_cursor_init_kernel(unsigned long long *cursor, int nb) {
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < nb) cursor[b] = (unsigned long long)b << IP_SHIFT;
+}
+
+__global__ void __launch_bounds__(IP_THREADS)
+    isa_partition_kernel(const uint32_t *__restrict__ sa, long m, int nb, unsigned long long *__restrict__ cursor,
+                         uint64_t *__restrict__ pairs) {
+  __shared__ uint32_t cnt[IP_MAX_BUCKETS];   // count, then running slot inside the tile
+  __shared__ uint32_t toff[IP_MAX_BUCKETS];  // first slot of the range inside the tile
+  __shared__ unsigned long long gofs[IP_MAX_BUCKETS];
+  __shared__ uint64_t stage[IP_TILE];
+  __shared__ uint32_t wsum[IP_THREADS / 32];
+  static_assert(IP_MAX_BUCKETS <= IP_THREADS, "one range per thread in the scan");
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long base = (long)blockIdx.x * IP_TILE;
+  const int valid = (int)min((long)IP_TILE, m - base);
+  for (int b = tid; b < nb; b += IP_THREADS) cnt[b] = 0;
+  __syncthreads();
+  uint32_t v[IP_ITEMS];
+#pragma unroll
+  for (int k = 0; k < IP_ITEMS; ++k) {
+    int e = tid + k * IP_THREADS;
+    v[k] = e < valid ? sa[base + e] : 0u;
+    if (e < valid) atomicAdd(&cnt[v[k] >> IP_SHIFT], 1u);
+  }
+  __syncthreads();
+  {
+    uint32_t c = tid < nb ? cnt[tid] : 0u, incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    uint32_t woff = 0;
+    for (int w = 0; w < warp; ++w) woff += wsum[w];
+    uint32_t ex = woff + incl - c;
+    if (tid < nb) {
+      toff[tid] = ex; cnt[tid] = ex;
+      if (c) gofs[tid] = atomicAdd(&cursor[tid], (unsigned long long)c);
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < IP_ITEMS; ++k) {
+    int e = tid + k * IP_THREADS;
+    if (e < valid) stage[atomicAdd(&cnt[v[k] >> IP_SHIFT], 1u)] = ((uint64_t)v[k] << 32) | (uint32_t)(base + e);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < IP_ITEMS; ++k) {
+    int e = tid + k * IP_THREADS;
+    if (e < valid) {
+      uint64_t x = stage[e];
+      int b = (int)(x >> (32 + IP_SHIFT));
+      pairs[gofs[b] + (unsigned long long)(e - toff[b])] = x;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    isa_from_pairs_kernel(const uint64_t *__restrict__ pairs, long m, uint32_t *__restrict__ isa) {
+  long i = ((long)blockIdx.x * blockDim.x + threadIdx.x) * 2;
+  if (i + 2 <= m) {
+    ulonglong2 x = *reinterpret_cast<const ulonglong2 *>(pairs + i);
+    isa[x.x >> 32] = (uint32_t)x.x;
+    isa[x.y >> 32] = (uint32_t)x.y;
+  } else if (i < m) {
+    uint64_t x = pairs[i];
+    isa[x >> 32] = (uint32_t)x;
+  }
+}
+
 __global__ void __launch_bounds__(256)
     isa_fix_kernel(const uint64_t *__restrict__ keyY, const uint32_t *__restrict__ valY, long a,
                    uint32_t *__restrict__ isa) {
@@ -396,7 +479,20 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
       if (res->isa.p == nullptr) {
         // first doubling round: now the full inverse suffix array is needed
         res->isa.alloc(ctx, m);
-        { KTrace kt(ctx, "isa_scatter"); isa_scatter_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(res->sa.p, m, res->isa.p); }
+        if (m >= (1L << 24)) {  // ISA larger than 64 MB: group by 16 MB range first (scratch: the free key buffer)
+          KTrace kt(ctx, "isa_scatter");
+          const int nb = (int)(((m - 1) >> IP_SHIFT) + 1);
+          uint64_t *pairs = kbuf[1 - out];
+          DevBuf<unsigned long long> cursor(ctx, IP_MAX_BUCKETS);
+          isa_cursor_init_kernel<<<div_up(nb, 256), 256, 0, ctx->stream>>>(cursor.p, nb);
+          isa_partition_kernel<<<(unsigned)div_up(m, IP_TILE), IP_THREADS, 0, ctx->stream>>>(res->sa.p, m, nb, cursor.p, pairs);
+          PSC_LAUNCH_CHECK();
+          isa_from_pairs_kernel<<<(unsigned)div_up(div_up(m, 2), 256), 256, 0, ctx->stream>>>(pairs, m, res->isa.p);
+          ctx->launches += 2;
+        } else {
+          KTrace kt(ctx, "isa_scatter");
+          isa_scatter_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(res->sa.p, m, res->isa.p);
+        }
         PSC_LAUNCH_CHECK();
         { KTrace kt(ctx, "isa_fix"); isa_fix_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, res->isa.p); }
         PSC_LAUNCH_CHECK();

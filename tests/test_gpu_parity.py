@@ -200,7 +200,9 @@ def sa_is_valid(text, sa):
 
 
 @pytest.mark.parametrize("gen,n,mb", [("dna", 3_000_000, 0), ("random", 2_000_000, 0),
-                                      ("markov", 1_500_000, 400_000), ("repetitive", 2_000_000, 700_001)])
+                                      ("markov", 1_500_000, 400_000), ("repetitive", 2_000_000, 700_001),
+                                      # blocks above 2^24: range-partitioned ISA scatter and rank stream
+                                      ("markov", 40_000_000, 18_000_000), ("repetitive", 20_000_000, 0)])
 def test_large_property_check(ctx, gen, n, mb):
     text = textgen.GENERATORS[gen](n)
     sa = decode_sa5(ctx.construct_sa(text, max_block=mb))
