@@ -50,9 +50,8 @@ struct RenameLut {
 // ---- round 0 keys --------------------------------------------------------------------------
 // keys[i] = the k renamed symbols at i, packed MSB first; also counts every 8-bit digit of the
 // keys (the radix sort's histogram), so the keys are not read again before the first pass.
-// Each thread builds the keys of PD_ITEMS consecutive positions with a rolling update (one code
-// read per position instead of k); the staged codes are padded by one word per 32 so that the
-// 16-byte thread stride does not collide on shared-memory banks.
+// The renamed codes of a tile are staged in shared memory once (the 256-entry code table too: indexed
+// per thread it must not sit in the constant bank, where 32 different indices serialise).
 __device__ __forceinline__ int code_slot(int e) { return e + ((e >> 6) << 1); }
 
 __global__ void __launch_bounds__(SC_THREADS)
@@ -61,7 +60,10 @@ __global__ void __launch_bounds__(SC_THREADS)
                      unsigned long long *__restrict__ ghist) {
   extern __shared__ uint16_t codes[];  // code_slot(PD_TILE + k) + 2, then 8 * 256 uint32 histogram
   uint32_t *sh = reinterpret_cast<uint32_t *>(codes + ((code_slot(PD_TILE + lut.k) + 3) & ~1));
+  __shared__ uint16_t scode[256];  // the table indexed per thread: shared memory, not the constant bank
   for (int e = threadIdx.x; e < 8 * 256; e += SC_THREADS) sh[e] = 0;
+  scode[threadIdx.x] = lut.code[threadIdx.x];
+  __syncthreads();
   const long t0 = (long)blockIdx.x * PD_TILE;
   const int span = PD_TILE + lut.k;
   for (int e = threadIdx.x; e < span; e += SC_THREADS) {
@@ -69,7 +71,7 @@ __global__ void __launch_bounds__(SC_THREADS)
     uint16_t cd = 0;
     if (i < m) {
       int c = text[i];
-      cd = lut.code[c];
+      cd = scode[c];
       if (c == lut.last && (i == m - 1 || gt_end == nullptr || bit_get(gt_end, i + 1)))
         cd = lut.code_last_high;
     }
@@ -78,28 +80,23 @@ __global__ void __launch_bounds__(SC_THREADS)
   __syncthreads();
   const int k = lut.k, bits = lut.bits;
   const uint64_t mask = (k * bits >= 64) ? ~0ull : ((1ull << (k * bits)) - 1ull);
-  const int e0 = threadIdx.x * PD_ITEMS;
-  uint64_t key = 0;
-  for (int j = 0; j < k - 1; ++j) key = (key << bits) | codes[code_slot(e0 + j)];
-  uint64_t out[PD_ITEMS];
+  // two consecutive positions per thread and step (rolling update for the second one): one 16-byte
+  // store per lane, a warp writes 512 contiguous bytes
 #pragma unroll
-  for (int q = 0; q < PD_ITEMS; ++q) {
-    key = ((key << bits) | codes[code_slot(e0 + k - 1 + q)]) & mask;
-    out[q] = key;
-  }
-  const long i0 = t0 + e0;
-  if (i0 + PD_ITEMS <= m) {
-    ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(keys + i0);
-#pragma unroll
-    for (int q = 0; q < PD_ITEMS; q += 2) dst[q / 2] = make_ulonglong2(out[q], out[q + 1]);
-  } else {
-#pragma unroll
-    for (int q = 0; q < PD_ITEMS; ++q) if (i0 + q < m) keys[i0 + q] = out[q];
-  }
-#pragma unroll
-  for (int q = 0; q < PD_ITEMS; ++q) {
-    if (i0 + q < m)
-      for (int p = 0; p < passes; ++p) atomicAdd(&sh[p * 256 + (int)((out[q] >> (8 * p)) & 255)], 1u);
+  for (int j = 0; j < PD_ITEMS / 2; ++j) {
+    const int e0 = 2 * (threadIdx.x + j * SC_THREADS);
+    const long i0 = t0 + e0;
+    if (i0 >= m) break;
+    uint64_t key = 0;
+    for (int q = 0; q < k; ++q) key = (key << bits) | codes[code_slot(e0 + q)];
+    const uint64_t k0 = key;
+    const uint64_t k1 = ((key << bits) | codes[code_slot(e0 + k)]) & mask;
+    if (i0 + 1 < m) *reinterpret_cast<ulonglong2 *>(keys + i0) = make_ulonglong2(k0, k1);
+    else keys[i0] = k0;
+    for (int p = 0; p < passes; ++p) {
+      atomicAdd(&sh[p * 256 + (int)((k0 >> (8 * p)) & 255)], 1u);
+      if (i0 + 1 < m) atomicAdd(&sh[p * 256 + (int)((k1 >> (8 * p)) & 255)], 1u);
+    }
   }
   __syncthreads();
   for (int e = threadIdx.x; e < passes * 256; e += SC_THREADS)
@@ -207,12 +204,12 @@ __global__ void __launch_bounds__(256)
 }
 
 __device__ __forceinline__ uint32_t renamed_code(const uint8_t *__restrict__ text, long m,
-                                                 const uint32_t *__restrict__ gt_end, const RenameLut &lut,
-                                                 long i) {
+                                                 const uint32_t *__restrict__ gt_end, const uint16_t *code,
+                                                 int last, uint32_t code_last_high, long i) {
   if (i >= m) return 0;
   int c = text[i];
-  if (c == lut.last && (i == m - 1 || gt_end == nullptr || bit_get(gt_end, i + 1))) return lut.code_last_high;
-  return lut.code[c];
+  if (c == last && (i == m - 1 || gt_end == nullptr || bit_get(gt_end, i + 1))) return code_last_high;
+  return code[c];
 }
 
 // next key straight from the text ("text round"): (group head << k1*bits) | the k1 renamed symbols
@@ -222,11 +219,15 @@ __global__ void __launch_bounds__(256)
     second_key_text_kernel(uint64_t *__restrict__ keyY, const uint32_t *__restrict__ valY, long a,
                            const uint8_t *__restrict__ text, long m, const uint32_t *__restrict__ gt_end,
                            RenameLut lut, long h, int k1) {
+  __shared__ uint16_t scode[256];
+  scode[threadIdx.x] = lut.code[threadIdx.x];
+  __syncthreads();
   long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= a) return;
   long p = (long)valY[j] + h;
   uint64_t key = keyY[j];
-  for (int s = 0; s < k1; ++s) key = (key << lut.bits) | renamed_code(text, m, gt_end, lut, p + s);
+  for (int s = 0; s < k1; ++s)
+    key = (key << lut.bits) | renamed_code(text, m, gt_end, scode, lut.last, lut.code_last_high, p + s);
   keyY[j] = key;
 }
 
@@ -408,8 +409,41 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
   long tiles = div_up(m, PD_TILE);
   DevBuf<unsigned long long> ghist(ctx, 8 * 256);
   ghist.zero();
+  // 8-bit codes: digit p of key(i) IS the code at i + k-1-p, so every digit histogram is the symbol
+  // histogram shifted by a few positions -- computed here instead of `passes` shared atomics per
+  // suffix in the kernel (8.2 -> 2.x ms for 2^30 random bytes)
+  const bool hist_on_host = (lut.bits == 8 && m >= 64);
+  std::vector<unsigned long long> gh;
+  if (hist_on_host) {
+    uint8_t head[8];
+    uint32_t gw = 0xffffffffu;
+    d2h(ctx, head, text_d, 8);
+    if (gt_end_bits_d) d2h(ctx, &gw, gt_end_bits_d, 1);
+    sync(ctx);
+    unsigned long long ch[256] = {0};
+    for (int c = 0; c < 256; ++c) {
+      if (c == last) {
+        if (hist[256]) ch[lut.code[c]] += hist[256];
+        ch[lut.code_last_high] += hist[c] - hist[256];
+      } else if (hist[c]) ch[lut.code[c]] += hist[c];
+    }
+    int hc[8];
+    for (int j = 0; j < 8; ++j) {
+      int c = head[j];
+      hc[j] = lut.code[c];
+      if (c == last && (gt_end_bits_d == nullptr || ((gw >> (j + 1)) & 1u))) hc[j] = lut.code_last_high;
+    }
+    gh.assign(8 * 256, 0);
+    for (int p = 0; p < passes; ++p) {
+      const int off = k - 1 - p;  // digit p covers positions [off, m + off); codes past the end are 0
+      for (int d = 0; d < 256; ++d) gh[p * 256 + d] = ch[d];
+      for (int j = 0; j < off; ++j) gh[p * 256 + hc[j]]--;
+      gh[p * 256 + 0] += (unsigned long long)off;
+    }
+    h2d(ctx, ghist.p, gh.data(), gh.size());
+  }
   { KTrace kt(ctx, "init_keys"); init_keys_kernel<<<(unsigned)tiles, SC_THREADS, (size_t)(PD_TILE + k + (PD_TILE + k) / 32 + 8) * sizeof(uint16_t) + 8 * 256 * 4, ctx->stream>>>(
-      text_d, m, gt_end_bits_d, lut, passes, keyA.p, ghist.p); }
+      text_d, m, gt_end_bits_d, lut, hist_on_host ? 0 : passes, keyA.p, ghist.p); }
   PSC_LAUNCH_CHECK();
   ctx->launches++;
   DevBuf<uint64_t> key_of_zero(ctx, 1), total_d(ctx, 1);
