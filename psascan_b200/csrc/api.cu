@@ -69,6 +69,7 @@ static size_t size_class(size_t bytes) {
 }
 
 void cache_trim(psc_context *ctx) {
+  std::lock_guard<std::mutex> lk(ctx->cache_mu);
   size_t k = 0;
   for (auto &b : ctx->cache) {
     if (b.used) ctx->cache[k++] = b;
@@ -80,15 +81,19 @@ void cache_trim(psc_context *ctx) {
 
 void *cache_alloc(psc_context *ctx, size_t bytes) {
   const size_t cls = size_class(bytes);
-  for (auto &b : ctx->cache)
-    if (!b.used && b.bytes == cls) { b.used = true; ctx->cache_free_bytes -= cls; return b.p; }
+  {
+    std::lock_guard<std::mutex> lk(ctx->cache_mu);
+    for (auto &b : ctx->cache)
+      if (!b.used && b.bytes == cls) { b.used = true; ctx->cache_free_bytes -= cls; return b.p; }
+  }
   void *q = nullptr;
   auto t0 = std::chrono::steady_clock::now();
   cudaError_t e = cudaMallocAsync(&q, cls, ctx->stream);
-  if (e == cudaErrorMemoryAllocation && ctx->cache_free_bytes) {  // unused classes hold the memory
+  if (e == cudaErrorMemoryAllocation) {  // unused size classes (of either context) hold the memory
     cudaGetLastError();
     cache_trim(ctx);
-    cudaStreamSynchronize(ctx->stream);
+    if (ctx->aux) cache_trim(ctx->aux);
+    cudaDeviceSynchronize();
     e = cudaMallocAsync(&q, cls, ctx->stream);
   }
   if (ctx->trace) {
@@ -100,11 +105,13 @@ void *cache_alloc(psc_context *ctx, size_t bytes) {
     set_error("device allocation of %zu bytes failed: %s", cls, cudaGetErrorString(e));
     throw CudaError{e == cudaErrorMemoryAllocation ? PSC_ENOMEM : PSC_ECUDA};
   }
+  std::lock_guard<std::mutex> lk(ctx->cache_mu);
   ctx->cache.push_back({q, cls, true});
   return q;
 }
 
 void cache_release(psc_context *ctx, void *p) {
+  std::lock_guard<std::mutex> lk(ctx->cache_mu);
   for (auto &b : ctx->cache)
     if (b.p == p) { b.used = false; ctx->cache_free_bytes += b.bytes; return; }
   cudaFreeAsync(p, ctx->stream);  // not ours (cannot happen)
@@ -123,8 +130,42 @@ void trace_report(psc_context *ctx) {
   ctx->trace_rows.clear();
 }
 
+// bytes this context may still use: free HBM + what the pool and the buffer caches hold unused
+double hbm_available(psc_context *ctx) {
+  size_t free_b = 0, total_b = 0;
+  if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); return 0; }
+  uint64_t reserved = 0, used = 0;
+  cudaMemPoolGetAttribute(ctx->pool, cudaMemPoolAttrReservedMemCurrent, &reserved);
+  cudaMemPoolGetAttribute(ctx->pool, cudaMemPoolAttrUsedMemCurrent, &used);
+  double avail = (double)free_b + (double)(reserved - used) + (double)ctx->cache_free_bytes +
+                 (ctx->aux ? (double)ctx->aux->cache_free_bytes : 0.0);
+  if (ctx->hbm_budget && (double)ctx->hbm_budget < avail) avail = (double)ctx->hbm_budget;
+  return avail * 0.92;
+}
+
+static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
+                                    uint8_t *out_sa5_d);
+
+// several blocks: sorts run ahead on a second stream (dist.cu); PSC_PIPELINE=0 keeps everything on one
 static void construct_sa_device(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
                                 uint8_t *out_sa5_d) {
+  if (n > 0) {
+    if (max_block <= 0) max_block = psc_max_block_size(ctx, n);
+    arg_check(max_block > 0, "text does not fit the HBM budget");
+    max_block = std::min(max_block, (1L << 31) - 4096);
+    static int pipe = -1;
+    if (pipe < 0) { const char *e = getenv("PSC_PIPELINE"); pipe = e ? atoi(e) : 1; }
+    if (pipe && div_up(n, max_block) > 1) {
+      // sorted-ahead blocks (2 x 5.2 B) + one block in the sorter (40 B) + one streaming (<= 45 B per symbol)
+      double need = 16.3 * (double)n + 8.0 * (double)std::min(n, 1L << 29) + 96.0 * (double)max_block;
+      if (need <= hbm_available(ctx)) { construct_sa_pipelined(ctx, text_d, n, max_block, out_sa5_d); return; }
+    }
+  }
+  construct_sa_sequential(ctx, text_d, n, max_block, out_sa5_d);
+}
+
+static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
+                                    uint8_t *out_sa5_d) {
   memset(&ctx->stats, 0, sizeof(ctx->stats));
   ctx->launches = 0;
   if (n == 0) return;
@@ -240,6 +281,14 @@ int psc_shutdown(psc_context *ctx) {
   if (!ctx) return PSC_OK;
   cudaSetDevice(ctx->device);
   cache_trim(ctx);
+  if (ctx->aux) {
+    cache_trim(ctx->aux);
+    cudaStreamSynchronize(ctx->aux->stream);
+    cudaStreamDestroy(ctx->aux->stream);
+    cudaStreamDestroy(ctx->aux->side);
+    delete ctx->aux;
+    ctx->aux = nullptr;
+  }
   cudaStreamSynchronize(ctx->stream);
   cudaMemPoolTrimTo(ctx->pool, 0);
   cudaStreamDestroy(ctx->stream);
@@ -250,18 +299,12 @@ int psc_shutdown(psc_context *ctx) {
 
 long psc_max_block_size(psc_context *ctx, long n) {
   if (!ctx || n <= 0) return 0;
-  size_t free_b = 0, total_b = 0;
   cudaSetDevice(ctx->device);
   cache_trim(ctx);
+  if (ctx->aux) { cache_trim(ctx->aux); cudaStreamSynchronize(ctx->aux->stream); }
   cudaStreamSynchronize(ctx->stream);
-  if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 0;
-  uint64_t reserved = 0;
-  cudaMemPoolGetAttribute(ctx->pool, cudaMemPoolAttrReservedMemCurrent, &reserved);
-  uint64_t used = 0;
-  cudaMemPoolGetAttribute(ctx->pool, cudaMemPoolAttrUsedMemCurrent, &used);
-  double avail = (double)free_b + (double)(reserved - used);
-  if (ctx->hbm_budget && (double)ctx->hbm_budget < avail) avail = (double)ctx->hbm_budget;
-  avail *= 0.92;
+  double avail = psc::hbm_available(ctx);
+  if (avail <= 0) return 0;
   // single block: text + output + 40 B/symbol of sort state
   if ((double)n * 52.0 <= avail && n <= (1L << 31) - 4096) return n;
   // multi block: text n + merged planes 10n + output 5n + gt bits; per block symbol: 40 B sort state,

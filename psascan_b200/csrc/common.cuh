@@ -6,6 +6,7 @@
 #include <string.h>
 #include <string>
 #include <chrono>
+#include <mutex>
 #include <vector>
 #include "../../include/psascan_cuda.h"
 
@@ -53,6 +54,10 @@ struct psc_context {
   struct CacheBlock { void *p; size_t bytes; bool used; };
   std::vector<CacheBlock> cache;
   size_t cache_free_bytes = 0;
+  std::mutex cache_mu;  // buffers of the sorter context are released by the streaming thread
+  // second context (own stream, own cache) on which block sorts run ahead of the walk/merge chain
+  psc_context *aux = nullptr;
+  int walk_threads_per_sm = 2048;
 };
 
 namespace psc {
@@ -257,6 +262,9 @@ void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, con
              const uint8_t *tail_d, long t, long lo, long nwalk, const uint64_t *walk_beg_d,
              const uint64_t *start_rank_d, const uint32_t *gt_in_bits_d, long gt_in_off,
              uint32_t *gt_out_bits_d, long gt_out_off, uint32_t *gap_d);
+
+// dist.cu: single-GPU schedule with the block sorts running ahead on a second stream
+void construct_sa_pipelined(psc_context *ctx, const uint8_t *text_d, long n, long max_block, uint8_t *out_sa5_d);
 
 // K5 + K6 over tail positions [lo, hi), chunked (walk.cu)
 void walk_tail_range(psc_context *ctx, const psc_rank *rk, long i0, uint8_t last, const uint64_t *Cmap,

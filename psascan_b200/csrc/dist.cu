@@ -9,7 +9,12 @@
 // Collectives are delegated to the caller through psc_collective_fn (torch.distributed in
 // psascan_b200/dist.py, NCCL over NVLink); the library synchronises its stream around them.
 #include <algorithm>
+#include <condition_variable>
+#include <deque>
 #include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
 #include "common.cuh"
 
 namespace psc {
@@ -36,9 +41,41 @@ struct OwnedBlock {
   DevBuf<uint32_t> gtb;  // bit q <-> block position q+1, q in [0, m-1)
   long i0 = 0;
   int end_bit = 0;       // gt bit of position `end` relative to the block begin
+  uint8_t last = 0;      // text[end - 1]
 };
 
 struct BlockMeta { long long i0; int end_bit; int last; };
+
+// K0 (by plain comparison past the block end) + block sort + gt_begin bits + BWT of text[beg, end):
+// everything a block contributes that does not depend on the blocks to its right.
+static std::unique_ptr<OwnedBlock> sort_owned_block(psc_context *ctx, const uint8_t *text_d, long n, long beg,
+                                                    long end) {
+  const long m = end - beg, t = n - end;
+  auto ob = std::make_unique<OwnedBlock>();
+  BlockSortResult res;
+  DevBuf<uint32_t> gt_end;
+  if (t > 0) {
+    gt_end.alloc(ctx, m / 32 + 2);
+    compute_gt_end(ctx, text_d + beg, m, text_d + end, t, 1, nullptr, 0, gt_end.p);
+  }
+  sort_block(ctx, text_d + beg, m, t > 0 ? gt_end.p : nullptr, &res);
+  res.isa.release();
+  ob->i0 = res.i0;
+  ob->gtb.alloc(ctx, m / 32 + 2);
+  ob->gtb.zero();
+  gt_begin_from_sa(ctx, res.sa.p, m, (uint32_t)res.i0, ob->gtb.p, 0);
+  uint32_t w0 = 1;  // gt_end[0]: 1 for the last block
+  if (t > 0) { d2h(ctx, &w0, gt_end.p, 1); sync(ctx); }
+  ob->end_bit = (w0 & 1u) ? 0 : 1;  // !gt_end[beg]  (change_gt_reference_point.hpp)
+  if (t > 0) {
+    ob->bwt.alloc(ctx, m);
+    bwt_from_sa(ctx, text_d + beg, res.sa.p, m, ob->bwt.p);
+  }
+  PSC_CUDA(cudaMemcpyAsync(&ob->last, text_d + end - 1, 1, cudaMemcpyDeviceToHost, ctx->stream));
+  ob->sa = std::move(res.sa);
+  sync(ctx);
+  return ob;
+}
 
 static void coll(psc_context *ctx, psc_collective_fn fn, void *user, int op, void *buf, size_t bytes, int root) {
   sync(ctx);
@@ -66,29 +103,7 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
     if (owner(id) != rank) continue;
     long beg, end;
     bounds(id, &beg, &end);
-    const long m = end - beg, t = n - end;
-    auto ob = std::make_unique<OwnedBlock>();
-    BlockSortResult res;
-    DevBuf<uint32_t> gt_end;
-    if (t > 0) {
-      gt_end.alloc(ctx, m / 32 + 2);
-      compute_gt_end(ctx, text_d + beg, m, text_d + end, t, 1, nullptr, 0, gt_end.p);
-    }
-    sort_block(ctx, text_d + beg, m, t > 0 ? gt_end.p : nullptr, &res);
-    res.isa.release();
-    ob->i0 = res.i0;
-    ob->gtb.alloc(ctx, m / 32 + 2);
-    ob->gtb.zero();
-    gt_begin_from_sa(ctx, res.sa.p, m, (uint32_t)res.i0, ob->gtb.p, 0);
-    uint32_t w0 = 1;  // gt_end[0]: 1 for the last block
-    if (t > 0) { d2h(ctx, &w0, gt_end.p, 1); sync(ctx); }
-    ob->end_bit = (w0 & 1u) ? 0 : 1;  // !gt_end[beg]  (change_gt_reference_point.hpp)
-    if (t > 0) {
-      ob->bwt.alloc(ctx, m);
-      bwt_from_sa(ctx, text_d + beg, res.sa.p, m, ob->bwt.p);
-    }
-    ob->sa = std::move(res.sa);
-    mine[id] = std::move(ob);
+    mine[id] = sort_owned_block(ctx, text_d, n, beg, end);
   }
 
   // ---- phase 2: right to left
@@ -115,10 +130,7 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
     BlockMeta meta{0, 0, 0};
     if (own == rank) {
       sa_p = ob->sa.p; gtb_p = ob->gtb.p; bwt_p = ob->bwt.p;
-      uint8_t last;
-      PSC_CUDA(cudaMemcpyAsync(&last, text_d + end - 1, 1, cudaMemcpyDeviceToHost, ctx->stream));
-      sync(ctx);
-      meta = BlockMeta{ob->i0, ob->end_bit, (int)last};
+      meta = BlockMeta{ob->i0, ob->end_bit, (int)ob->last};
     } else {
       sa_tmp.alloc(ctx, m); gtb_tmp.alloc(ctx, m / 32 + 2);
       sa_p = sa_tmp.p; gtb_p = gtb_tmp.p;
@@ -178,6 +190,159 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
   pack_sa5(ctx, Mlo[cur].p, Mhi[cur].p, n, out_sa5_d);
   sync(ctx);
   ctx->stats.kernel_launches = ctx->launches;
+}
+
+// ---- one GPU, two streams -------------------------------------------------------------------------
+// The same two phases overlapped on ONE device: a sorter thread with its own context (stream, buffer
+// cache) sorts blocks right to left and runs at most PIPE_DEPTH blocks ahead; the calling thread
+// streams each sorted block through rank build, LF walk and merge.  The walk is bound by the HBM's
+// random-access rate; the sort kernels of the next blocks fill the gaps around it (rank build,
+// partition, accumulate, merge, host round trips).  Measured gain on 8 x 128 MiB: 274 -> 264 ms; it
+// costs the memory of the blocks sorted ahead, so api.cu only takes this path when HBM allows.
+constexpr int PIPE_DEPTH = 2;
+
+struct SortQueue {
+  std::mutex mu;
+  std::condition_variable cv;
+  std::deque<std::unique_ptr<OwnedBlock>> ready;
+  long consumed = 0, produced = 0;
+  bool failed = false, cancel = false;
+  int fail_code = 0;
+  std::string fail_msg;
+};
+
+static psc_context *aux_context(psc_context *ctx) {
+  if (ctx->aux) return ctx->aux;
+  psc_context *a = new psc_context();
+  a->device = ctx->device;
+  a->n_sm = ctx->n_sm;
+  a->pool = ctx->pool;
+  a->trace = ctx->trace;
+  PSC_CUDA(cudaStreamCreateWithFlags(&a->stream, cudaStreamNonBlocking));
+  PSC_CUDA(cudaStreamCreateWithFlags(&a->side, cudaStreamNonBlocking));
+  memset(&a->stats, 0, sizeof(a->stats));
+  ctx->aux = a;
+  return a;
+}
+
+void construct_sa_pipelined(psc_context *ctx, const uint8_t *text_d, long n, long max_block, uint8_t *out_sa5_d) {
+  memset(&ctx->stats, 0, sizeof(ctx->stats));
+  ctx->launches = 0;
+  if (n == 0) return;
+  psc_context *aux = aux_context(ctx);
+  memset(&aux->stats, 0, sizeof(aux->stats));
+  aux->launches = 0;
+  PhaseTimer total(ctx, &ctx->stats.ms_total);
+  max_block = std::min(max_block, (1L << 31) - 4096);
+  const long B = div_up(n, max_block);
+  ctx->stats.n_blocks = B;
+  auto bounds = [&](long id, long *beg, long *end) { *beg = id * max_block; *end = std::min(n, *beg + max_block); };
+
+  SortQueue q;
+  std::thread sorter([&] {
+    try {
+      PSC_CUDA(cudaSetDevice(aux->device));
+      for (long id = B - 1; id >= 0; --id) {
+        {
+          std::unique_lock<std::mutex> lk(q.mu);
+          q.cv.wait(lk, [&] { return q.cancel || q.produced - q.consumed < PIPE_DEPTH; });
+          if (q.cancel) return;
+        }
+        long beg, end;
+        bounds(id, &beg, &end);
+        auto ob = sort_owned_block(aux, text_d, n, beg, end);
+        std::lock_guard<std::mutex> lk(q.mu);
+        q.ready.push_back(std::move(ob));
+        q.produced++;
+        q.cv.notify_all();
+      }
+    } catch (const CudaError &e) {
+      std::lock_guard<std::mutex> lk(q.mu);
+      q.failed = true;
+      q.fail_code = e.code;
+      q.fail_msg = psc_last_error();
+      q.cv.notify_all();
+    }
+  });
+  struct Joiner {  // the sorter must be gone before the queue or any buffer is
+    SortQueue &q; std::thread &t;
+    ~Joiner() { { std::lock_guard<std::mutex> lk(q.mu); q.cancel = true; q.cv.notify_all(); } if (t.joinable()) t.join(); }
+  } joiner{q, sorter};
+
+  const int walkers_before = ctx->walk_threads_per_sm;
+  {  // measured on B200: fewer walkers per SM do not let more sort CTAs in, they only slow the walk
+    const char *e = getenv("PSC_PIPE_WALK_TPS");
+    ctx->walk_threads_per_sm = e ? atoi(e) : 2048;
+  }
+  struct Restore { psc_context *c; int v; ~Restore() { c->walk_threads_per_sm = v; } } restore{ctx, walkers_before};
+
+  const long gwords = (n + 1 + 31) / 32 + 2;
+  DevBuf<uint32_t> Ga(ctx, gwords), Gb(ctx, gwords);
+  Ga.zero(); Gb.zero();
+  uint32_t *gt_cur = Ga.p, *gt_new = Gb.p;
+  DevBuf<uint32_t> Mlo[2];
+  DevBuf<uint8_t> Mhi[2];
+  for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); Mhi[k].alloc(ctx, n); }
+  int cur = 0;
+  long right_len = 0;
+  for (long id = B - 1; id >= 0; --id) {
+    long beg, end;
+    bounds(id, &beg, &end);
+    const long m = end - beg, t = n - end;
+    std::unique_ptr<OwnedBlock> ob;
+    {
+      std::unique_lock<std::mutex> lk(q.mu);
+      q.cv.wait(lk, [&] { return q.failed || !q.ready.empty(); });
+      if (q.failed) { set_error("%s", q.fail_msg.c_str()); throw CudaError{q.fail_code}; }
+      ob = std::move(q.ready.front());
+      q.ready.pop_front();
+    }
+    PSC_CUDA(cudaMemsetAsync(gt_new, 0, gwords * 4, ctx->stream));
+    DevBuf<uint32_t> gap;
+    if (t > 0) {
+      gap.alloc(ctx, m + 1);
+      gap.zero();
+      psc_rank *rk = rank_build(ctx, ob->bwt.p, m, ob->i0);
+      try {
+        uint64_t Cmap[256], run = 0;
+        for (int c = 0; c < 256; ++c) { Cmap[c] = run; run += (uint64_t)rk->counts[c] + (c == ob->last ? 1 : 0); }
+        walk_tail_range(ctx, rk, ob->i0, ob->last, Cmap, text_d + beg, ob->sa.p, m, text_d + end, t, 0, t, gt_cur, end,
+                        id > 0 ? gt_new : nullptr, gap.p);
+      } catch (...) { rank_free(rk); throw; }
+      rank_free(rk);
+    }
+    if (id > 0) {
+      if (m > 1) {
+        or_bits_shifted_kernel<<<(unsigned)div_up(div_up(m - 1, 32), 256), 256, 0, ctx->stream>>>(gt_new, beg, ob->gtb.p, m - 1);
+        PSC_LAUNCH_CHECK();
+      }
+      if (ob->end_bit) { set_bit_kernel<<<1, 1, 0, ctx->stream>>>(gt_new, end - 1); PSC_LAUNCH_CHECK(); }
+      ctx->launches += 2;
+    }
+    int nxt = 1 - cur;
+    merge_level(ctx, ob->sa.p, gap.p, m, beg, Mlo[cur].p, Mhi[cur].p, right_len, Mlo[nxt].p, Mhi[nxt].p);
+    cur = nxt;
+    right_len += m;
+    std::swap(gt_cur, gt_new);
+    sync(ctx);   // the block's buffers go back to the sorter's cache: nothing of ours may still read them
+    ob.reset();
+    {
+      std::lock_guard<std::mutex> lk(q.mu);
+      q.consumed++;
+      q.cv.notify_all();
+    }
+  }
+  pack_sa5(ctx, Mlo[cur].p, Mhi[cur].p, n, out_sa5_d);
+  sync(ctx);
+  // the sorter's counters belong to the same construction
+  const psc_stats &a = aux->stats;
+  ctx->stats.ms_gt_end += a.ms_gt_end; ctx->stats.ms_sort += a.ms_sort; ctx->stats.ms_radix += a.ms_radix;
+  ctx->stats.ms_bwt += a.ms_bwt; ctx->stats.ms_radix_pass += a.ms_radix_pass;
+  ctx->stats.radix_passes += a.radix_passes; ctx->stats.radix_elems += a.radix_elems;
+  ctx->stats.doubling_rounds += a.doubling_rounds;
+  ctx->stats.kernel_launches = ctx->launches + aux->launches;
+  for (auto &r : aux->trace_rows) ctx->trace_rows.push_back(r);
+  aux->trace_rows.clear();
 }
 
 }  // namespace psc

@@ -293,7 +293,7 @@ void walk_tail_range(psc_context *ctx, const psc_rank *rk, long i0, uint8_t last
     const char *w = getenv("PSC_WALKERS");
     target_env = w ? std::max(1L, atol(w)) : 0;
   }
-  const long target = target_env > 0 ? target_env : (long)ctx->n_sm * 2048;
+  const long target = target_env > 0 ? target_env : (long)ctx->n_sm * ctx->walk_threads_per_sm;
   std::vector<uint64_t> wb;
   for (long clo = lo; clo < hi; clo += chunk) {
     const long chi = std::min(hi, clo + chunk);
