@@ -197,8 +197,11 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
 // cache) sorts blocks right to left and runs at most PIPE_DEPTH blocks ahead; the calling thread
 // streams each sorted block through rank build, LF walk and merge.  The walk is bound by the HBM's
 // random-access rate; the sort kernels of the next blocks fill the gaps around it (rank build,
-// partition, accumulate, merge, host round trips).  Measured gain on 8 x 128 MiB: 274 -> 264 ms; it
-// costs the memory of the blocks sorted ahead, so api.cu only takes this path when HBM allows.
+// partition, accumulate, merge, host round trips).  While a walk kernel and a radix pass do run side
+// by side (512 walkers per SM leave room for a sort CTA) they contend for the same HBM: the walk
+// slows from 98 to 129 ms and the passes from 41 to 106 ms, so the gain on 8 x 128 MiB is modest
+// (274 -> 264 ms); it costs the memory of the blocks sorted ahead, so api.cu only takes this path
+// when HBM allows.
 constexpr int PIPE_DEPTH = 2;
 
 struct SortQueue {
@@ -270,10 +273,7 @@ void construct_sa_pipelined(psc_context *ctx, const uint8_t *text_d, long n, lon
   } joiner{q, sorter};
 
   const int walkers_before = ctx->walk_threads_per_sm;
-  {  // measured on B200: fewer walkers per SM do not let more sort CTAs in, they only slow the walk
-    const char *e = getenv("PSC_PIPE_WALK_TPS");
-    ctx->walk_threads_per_sm = e ? atoi(e) : 2048;
-  }
+  if (const char *e = getenv("PSC_PIPE_WALK_TPS")) ctx->walk_threads_per_sm = atoi(e);
   struct Restore { psc_context *c; int v; ~Restore() { c->walk_threads_per_sm = v; } } restore{ctx, walkers_before};
 
   const long gwords = (n + 1 + 31) / 32 + 2;

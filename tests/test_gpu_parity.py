@@ -224,3 +224,23 @@ def test_dist_schedule_single_rank(ctx):
             ctx.construct_sa_dist_ptr(d_text.data_ptr(), n, d_out.data_ptr(), mb)
             torch.cuda.synchronize()
             assert np.array_equal(d_out.cpu().numpy(), sa5), (name, mb)
+
+
+def test_pipelined_schedule_subprocess():
+    """PSC_PIPELINE=1 (block sorts running ahead on a second stream, csrc/dist.cu) is read once per
+    process, so it is exercised in a child: every multi-block golden case must come out bit-exact."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import psascan_b200 as P\n"
+        "from golden_cases import golden_cases, golden_text\n"
+        "c = P.Context(0)\n"
+        "for name, gen, kw, n, sa5 in golden_cases():\n"
+        "    t = golden_text(gen, kw, n)\n"
+        "    for mb in (n // 3 + 1, 1000):\n"
+        "        assert np.array_equal(c.construct_sa(t, max_block=mb), sa5), (name, mb)\n"
+        "print('pipelined ok', c.stats()['n_blocks'])\n" % (root, os.path.join(root, "tests")))
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, PSC_PIPELINE="1"),
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "pipelined ok" in r.stdout, r.stderr[-2000:]
