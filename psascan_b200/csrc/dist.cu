@@ -113,7 +113,7 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
   uint32_t *gt_cur = Ga.p, *gt_new = Gb.p;
   DevBuf<uint32_t> Mlo[2];
   DevBuf<uint8_t> Mhi[2];
-  for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); Mhi[k].alloc(ctx, n); }
+  for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); if (n > (1L << 32)) Mhi[k].alloc(ctx, n);  /* high bytes only above 4 GiB */ }
   DevBuf<BlockMeta> meta_d(ctx, 1);
   int cur = 0;
   long right_len = 0;
@@ -282,7 +282,7 @@ void construct_sa_pipelined(psc_context *ctx, const uint8_t *text_d, long n, lon
   uint32_t *gt_cur = Ga.p, *gt_new = Gb.p;
   DevBuf<uint32_t> Mlo[2];
   DevBuf<uint8_t> Mhi[2];
-  for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); Mhi[k].alloc(ctx, n); }
+  for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); if (n > (1L << 32)) Mhi[k].alloc(ctx, n);  /* high bytes only above 4 GiB */ }
   int cur = 0;
   long right_len = 0;
   for (long id = B - 1; id >= 0; --id) {

@@ -11,7 +11,7 @@
 
 namespace psc {
 
-constexpr int MG_ITEMS = 8;
+constexpr int MG_ITEMS = 32;
 constexpr int MG_TILE = SC_THREADS * MG_ITEMS;  // outputs per block
 
 // E[0..m] exclusive scan of gap[0..m];  A(u) = u + E[u] = output slot where run u starts
@@ -34,6 +34,8 @@ __global__ void __launch_bounds__(256)
   tile_u0[tile] = (uint32_t)lo;
 }
 
+// HI = false: every position is below 2^32 (text of at most 4 GiB), the high-byte plane does not exist.
+template <bool HI>
 __global__ void __launch_bounds__(SC_THREADS)
     merge_level_kernel(const uint32_t *__restrict__ sa, const uint64_t *__restrict__ E,
                        const uint32_t *__restrict__ tile_u0, long m, uint64_t beg, const uint32_t *__restrict__ right_lo,
@@ -78,10 +80,11 @@ __global__ void __launch_bounds__(SC_THREADS)
       v = beg + sa[u0 + nb];
     } else {
       uint64_t r = (uint64_t)q - (uint64_t)(u0 + nb);  // block suffixes before slot q: u0 + nb
-      v = (uint64_t)right_lo[r] | ((uint64_t)right_hi[r] << 32);
+      v = (uint64_t)right_lo[r];
+      if (HI) v |= (uint64_t)right_hi[r] << 32;
     }
     out_lo[q] = (uint32_t)v;
-    out_hi[q] = (uint8_t)(v >> 32);
+    if (HI) out_hi[q] = (uint8_t)(v >> 32);
   }
 }
 
@@ -92,7 +95,7 @@ __global__ void __launch_bounds__(256)
   if (i >= m) return;
   uint64_t v = beg + sa[i];
   lo[i] = (uint32_t)v;
-  hi[i] = (uint8_t)(v >> 32);
+  if (hi) hi[i] = (uint8_t)(v >> 32);
 }
 
 void merge_level(psc_context *ctx, const uint32_t *sa_d, const uint32_t *gap_d, long m, long beg,
@@ -114,8 +117,15 @@ void merge_level(psc_context *ctx, const uint32_t *sa_d, const uint32_t *gap_d, 
   { KTrace kt(ctx, "merge_tile_start"); merge_tile_start_kernel<<<(unsigned)div_up(ntiles, 256), 256, 0, ctx->stream>>>(E.p, m, ntiles, tile_u0.p); }
   PSC_LAUNCH_CHECK();
   ctx->launches++;
-  { KTrace kt(ctx, "merge_level"); merge_level_kernel<<<(unsigned)ntiles, SC_THREADS, 0, ctx->stream>>>(
-      sa_d, E.p, tile_u0.p, m, (uint64_t)beg, right_lo, right_hi, total, out_lo, out_hi); }
+  {
+    KTrace kt(ctx, "merge_level");
+    if (out_hi)
+      merge_level_kernel<true><<<(unsigned)ntiles, SC_THREADS, 0, ctx->stream>>>(
+          sa_d, E.p, tile_u0.p, m, (uint64_t)beg, right_lo, right_hi, total, out_lo, out_hi);
+    else
+      merge_level_kernel<false><<<(unsigned)ntiles, SC_THREADS, 0, ctx->stream>>>(
+          sa_d, E.p, tile_u0.p, m, (uint64_t)beg, right_lo, right_hi, total, out_lo, out_hi);
+  }
   PSC_LAUNCH_CHECK();
   ctx->launches++;
 }
@@ -129,7 +139,7 @@ __global__ void __launch_bounds__(256)
   if (i >= n) return;
   if (i + 4 <= n) {
     uint4 l = *reinterpret_cast<const uint4 *>(lo + i);
-    uint32_t h = *reinterpret_cast<const uint32_t *>(hi + i);
+    uint32_t h = hi ? *reinterpret_cast<const uint32_t *>(hi + i) : 0u;
     uint32_t h0 = h & 255, h1 = (h >> 8) & 255, h2 = (h >> 16) & 255, h3 = h >> 24;
     uint32_t *o = out_words + g * 5;
     o[0] = l.x;
@@ -142,7 +152,7 @@ __global__ void __launch_bounds__(256)
       uint32_t l = lo[k];
       uint8_t *o = out_bytes + k * 5;
       o[0] = (uint8_t)l; o[1] = (uint8_t)(l >> 8); o[2] = (uint8_t)(l >> 16); o[3] = (uint8_t)(l >> 24);
-      o[4] = hi[k];
+      o[4] = hi ? hi[k] : (uint8_t)0;
     }
   }
 }
