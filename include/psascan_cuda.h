@@ -29,6 +29,7 @@ extern "C" {
 #define PSC_ECUDA (-2)     /* CUDA runtime error / no device */
 #define PSC_ESENTINEL (-3) /* byte 255 in the text (initial_partial_sufsort.hpp:70-75) */
 #define PSC_ENOMEM (-4)    /* HBM budget exceeded */
+#define PSC_ELIMIT (-5)    /* work guard: repeats far longer than expected span a block boundary */
 
 typedef struct psc_context psc_context; /* one GPU, its streams and scratch memory */
 typedef struct psc_rank psc_rank;       /* device rank structure over one block BWT */

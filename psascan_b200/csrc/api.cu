@@ -59,6 +59,34 @@ static void gap_of_block(psc_context *ctx, const uint8_t *block_d, long m, const
   rank_free(rk);
 }
 
+// ---- work guard --------------------------------------------------------------------------------
+WorkBudget *work_budget_arm(psc_context *ctx) {
+  static unsigned long long limit = 0;
+  if (!limit) {
+    const char *e = getenv("PSC_COMPARE_BUDGET");
+    limit = e ? strtoull(e, nullptr, 10) : (1ull << 42);  // matched bytes per kernel (~ seconds on a B200)
+    if (!limit) limit = 1;
+  }
+  WorkBudget *wb = (WorkBudget *)cache_alloc(ctx, sizeof(WorkBudget));
+  WorkBudget h{0, limit, 0, 0};
+  cudaMemcpyAsync(wb, &h, sizeof(h), cudaMemcpyHostToDevice, ctx->stream);
+  cudaStreamSynchronize(ctx->stream);  // h is a stack object
+  return wb;
+}
+
+void work_budget_check(psc_context *ctx, WorkBudget *wb, const char *what) {
+  WorkBudget h;
+  cudaError_t e = cudaMemcpyAsync(&h, wb, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  cache_release(ctx, wb);
+  if (e != cudaSuccess) { set_error("%s: %s", what, cudaGetErrorString(e)); throw CudaError{PSC_ECUDA}; }
+  if (h.exceeded) {
+    set_error("%s: more than %llu matched bytes between block suffixes and the text after the block "
+              "(degenerate repeats across a block boundary); use one block or a larger max_block", what, h.limit);
+    throw CudaError{PSC_ELIMIT};
+  }
+}
+
 // ---- buffer cache ------------------------------------------------------------------------------
 static size_t size_class(size_t bytes) {
   // 16 classes per octave (<= 6.25 % slack), at least 512-byte steps

@@ -139,6 +139,10 @@ struct KTrace {
   }
 };
 void trace_report(psc_context *ctx);
+// device-side work guard (see WorkBudget below): allocate + arm, and check after the kernel
+struct WorkBudget;
+WorkBudget *work_budget_arm(psc_context *ctx);
+void work_budget_check(psc_context *ctx, WorkBudget *wb, const char *what);
 
 template <typename T>
 static inline void h2d(psc_context *ctx, T *dst, const T *src, size_t n) {
@@ -173,6 +177,29 @@ __device__ __forceinline__ void store_bits_word(uint32_t *bits, long bitpos, uin
   if (word << sh) atomicOr(&bits[w], word << sh);
   if (sh && (word >> (32 - sh))) atomicOr(&bits[w + 1], word >> (32 - sh));
 }
+// Work guard for the two brute-force comparisons of the path (K0 and the initial-rank binary search):
+// they are linear in the LCP between a block suffix and the text after the block, which is short on
+// every text but degenerate ones (period far below the block length).  Every 4 KiB of matched
+// symbols are charged to a device counter; past the limit the kernels bail out and the host reports
+// PSC_ELIMIT instead of hanging the GPU for hours.
+struct WorkBudget { unsigned long long used, limit; int exceeded; int pad; };
+
+__device__ __forceinline__ long common_prefix_guarded(const uint8_t *a, const uint8_t *b, long lim, WorkBudget *wb) {
+  long el = 0;
+  while (el < lim) {
+    const long stop = min(lim, el + 4096);
+    while (el < stop) {
+      uint32_t x = load_u32_any(a + el) ^ load_u32_any(b + el);
+      if (x) { el += (__ffs(x) - 1) >> 3; return el > lim ? lim : el; }
+      el += 4;
+    }
+    if (el < lim) {
+      if (atomicAdd(&wb->used, 4096ull) > wb->limit || *(volatile int *)&wb->exceeded) { wb->exceeded = 1; return -1; }
+    }
+  }
+  return el > lim ? lim : el;
+}
+
 // length of the common prefix of a[0..lim) and b[0..lim)
 __device__ __forceinline__ long common_prefix(const uint8_t *a, const uint8_t *b, long lim) {
   long el = 0;

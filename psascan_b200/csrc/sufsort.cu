@@ -554,15 +554,16 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
 __global__ void __launch_bounds__(256)
     gt_end_kernel(const uint8_t *__restrict__ block, long m, const uint8_t *__restrict__ after,
                   long after_len, int after_is_text_end, const uint32_t *__restrict__ gt_after,
-                  long gt_after_off, uint32_t *__restrict__ out_bits) {
+                  long gt_after_off, uint32_t *__restrict__ out_bits, WorkBudget *wb) {
   // gt_after == nullptr: the match simply continues past the block end into `after` (the block and
   // the text after it are contiguous), so no gt bits of the next block are needed.
   long p = (long)blockIdx.x * blockDim.x + threadIdx.x;
   bool g = false;
   if (p < m) {
     long lim = gt_after ? min(m - p, after_len) : after_len;
-    long el = common_prefix(block + p, after, lim);
-    if (el == after_len && after_is_text_end) g = true;
+    long el = common_prefix_guarded(block + p, after, lim, wb);
+    if (el < 0) g = false;  // work guard tripped: the host discards the result
+    else if (el == after_len && after_is_text_end) g = true;
     else if (gt_after && p + el == m) g = !bit_get(gt_after, gt_after_off + el - 1);
     else g = block[p + el] > after[el];
   }
@@ -575,10 +576,12 @@ void compute_gt_end(psc_context *ctx, const uint8_t *block_d, long m, const uint
                     long gt_after_off, uint32_t *gt_end_bits_d) {
   PhaseTimer timer(ctx, &ctx->stats.ms_gt_end);
   if (m == 0) return;
+  WorkBudget *wb = work_budget_arm(ctx);
   gt_end_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(
-      block_d, m, after_d, after_len, after_is_text_end, gt_after_bits_d, gt_after_off, gt_end_bits_d);
+      block_d, m, after_d, after_len, after_is_text_end, gt_after_bits_d, gt_after_off, gt_end_bits_d, wb);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
+  work_budget_check(ctx, wb, "gt_end (K0)");
 }
 
 // ---- K3: BWT and gt_begin ------------------------------------------------------------------------

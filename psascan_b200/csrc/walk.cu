@@ -20,7 +20,7 @@ __global__ void __launch_bounds__(128)
     initial_ranks_kernel(const uint8_t *__restrict__ block, const uint32_t *__restrict__ sa, long m,
                          const uint8_t *__restrict__ after, long after_len, int after_is_text_end,
                          const uint32_t *__restrict__ gt_after, long gt_after_off, long nstarts,
-                         const uint64_t *__restrict__ starts, uint64_t *__restrict__ out) {
+                         const uint64_t *__restrict__ starts, uint64_t *__restrict__ out, WorkBudget *wb) {
   long k = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= nstarts) return;
   long st = (long)starts[k];
@@ -33,7 +33,8 @@ __global__ void __launch_bounds__(128)
     long s = sa[mid];
     long slen = m - s;
     long lim = slen < plen ? slen : plen;
-    long lcp = common_prefix(block + s, pat, lim);
+    long lcp = common_prefix_guarded(block + s, pat, lim, wb);
+    if (lcp < 0) { out[k] = 0; return; }  // work guard tripped: the host discards the result
     bool pat_greater;
     if (lcp == slen) pat_greater = bit_get(gt_after, gt_after_off + st + slen - 1);  // :66-68
     else if (lcp == plen) pat_greater = false;                                       // :69-71
@@ -49,11 +50,13 @@ void initial_ranks(psc_context *ctx, const uint8_t *block_d, const uint32_t *sa_
                    const uint64_t *starts_d, uint64_t *out_d) {
   PhaseTimer timer(ctx, &ctx->stats.ms_init_ranks);
   if (nstarts <= 0) return;
+  WorkBudget *wb = work_budget_arm(ctx);
   initial_ranks_kernel<<<(unsigned)div_up(nstarts, 128), 128, 0, ctx->stream>>>(
       block_d, sa_d, m, after_d, after_len, after_is_text_end, gt_after_bits_d, gt_after_off, nstarts,
-      starts_d, out_d);
+      starts_d, out_d, wb);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
+  work_budget_check(ctx, wb, "initial ranks (K5)");
 }
 
 // ---- K6 ---------------------------------------------------------------------------------------

@@ -244,3 +244,27 @@ def test_pipelined_schedule_subprocess():
     r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, PSC_PIPELINE="1"),
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "pipelined ok" in r.stdout, r.stderr[-2000:]
+
+
+def test_work_guard_subprocess():
+    """K0 and the initial-rank search are linear in the LCP across the block boundary; a device-side
+    work guard turns a degenerate text into PSC_ELIMIT (-5) instead of a multi-hour kernel.  With the
+    default budget the same text must still come out right."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import psascan_b200 as P\n"
+        "from psascan_b200.lib import PscError, decode_sa5\n"
+        "t = np.full(300000, 65, dtype=np.uint8)\n"
+        "c = P.Context(0)\n"
+        "try:\n"
+        "    c.construct_sa(t, max_block=100000)\n"
+        "    print('no error')\n"
+        "except PscError as e:\n"
+        "    print('code', e.code)\n" % (root, os.path.join(root, "tests")))
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, PSC_COMPARE_BUDGET="65536"),
+                       capture_output=True, text=True, timeout=600)
+    assert "code -5" in r.stdout, (r.stdout, r.stderr[-1500:])
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ), capture_output=True, text=True, timeout=600)
+    assert "no error" in r.stdout, (r.stdout, r.stderr[-1500:])
