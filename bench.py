@@ -265,8 +265,10 @@ def main():
                 roof["r32_error"] = str(e)[:100]
         else:
             roof = {"kernel": "radix_pass_kernel", "bound": "hbm", "unit": "GB/s",
-                    "achieved": 24.0 * s["radix_elems"] / (s["ms_radix_pass"] / 1e3) / 1e9 if s["ms_radix_pass"] else None,
-                    "algorithmic_bytes_per_unit": 24.0, "units": "(key64,val32) pairs per digit pass",
+                    "achieved": s["radix_bytes"] / (s["ms_radix_pass"] / 1e3) / 1e9 if s["ms_radix_pass"] else None,
+                    "algorithmic_bytes_per_unit": s["radix_bytes"] / max(1, s["radix_elems"]),
+                    "units": "elements per digit pass (24 B per (key64,val32) pair, 16 B keys only, 9 B when the "
+                             "pass builds its keys from the text)",
                     "launches_per_step": s["radix_passes"],
                     "avg_launch_ms": s["ms_radix_pass"] / max(1, s["radix_passes"]),
                     "peak": peak, "peak_source": peak_src, "traffic": None}

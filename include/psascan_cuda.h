@@ -150,6 +150,8 @@ typedef struct psc_stats {
       ms_merge, ms_h2d, ms_d2h,
       ms_radix_pass; /* device time of the digit-pass kernels alone (events around each launch) */
   long n_blocks, lf_steps, radix_passes, radix_elems, doubling_rounds, walkers, kernel_launches;
+  long radix_bytes; /* algorithmic bytes of the digit passes: 12 in + 12 out per (key64, val32) pair, 8 + 8 for a
+                     * keys-only pass, 1 in for a pass that builds its keys from the text */
 } psc_stats;
 int psc_get_stats(psc_context *ctx, psc_stats *out);
 

@@ -161,11 +161,13 @@ int psc_bench_radix_pass(psc_context *ctx, long n, int iters, double *ms_per_pas
     PSC_LAUNCH_CHECK();
     int shifts[1] = {0};
     uint64_t *ko; uint32_t *vo;
-    radix_sort_pairs(ctx, ka.p, va.p, kb.p, vb.p, n, shifts, 1, &ko, &vo);  // warm-up
+    const bool keys_only = getenv("PSC_BENCH_KEYS_ONLY") != nullptr;  // 16 B per element instead of 24
+    uint32_t *v0 = keys_only ? nullptr : va.p, *v1 = keys_only ? nullptr : vb.p;
+    radix_sort_pairs(ctx, ka.p, v0, kb.p, v1, n, shifts, 1, &ko, keys_only ? nullptr : &vo);  // warm-up
     double before = ctx->stats.ms_radix_pass;
     for (int k = 0; k < iters; ++k) {
       shifts[0] = 8 * (k % 8);
-      radix_sort_pairs(ctx, ka.p, va.p, kb.p, vb.p, n, shifts, 1, &ko, &vo);
+      radix_sort_pairs(ctx, ka.p, v0, kb.p, v1, n, shifts, 1, &ko, keys_only ? nullptr : &vo);
     }
     *ms_per_pass = (ctx->stats.ms_radix_pass - before) / iters;
     return PSC_OK;

@@ -155,6 +155,15 @@ static inline void d2h(psc_context *ctx, T *dst, const T *src, size_t n) {
 static inline void sync(psc_context *ctx) { PSC_CUDA(cudaStreamSynchronize(ctx->stream)); }
 
 #ifdef __CUDACC__
+// relaxed device-scope accesses for look-back chains (status word = flag bits | payload)
+__device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t *p) {
+  uint64_t v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(uint64_t *p, uint64_t v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 __device__ __forceinline__ bool bit_get(const uint32_t *bits, long i) {
   return (bits[i >> 5] >> (i & 31)) & 1u;
 }
@@ -217,11 +226,24 @@ __device__ __forceinline__ long common_prefix(const uint8_t *a, const uint8_t *b
 // radix.cu: LSD onesweep sort of (key64, val32) pairs on the digit list `shifts` (8-bit
 // digits, least significant first).  Result pointers are returned in *keys_out / *vals_out
 // (one of the two buffer pairs).  Passes whose digit is constant over all keys are skipped.
+// vals_a == nullptr: keys only (the caller keeps its payload in the low key bits).
+// kg != nullptr: the first digit pass builds the keys from the text instead of reading keys_a.
+struct KeyGen {
+  const uint8_t *text;     // m symbols
+  const uint32_t *gt_end;  // renaming bits (may be null)
+  long m;
+  int last, code_last_high;
+  int dshift;  // digit of the first pass = (B >> dshift) & 255, B = the 8 renamed codes at the position, MSB first
+  int kshift;  // stored key = B >> kshift ...
+  int vbits;   // ... << vbits | position when vbits > 0
+  uint8_t code[256];  // 8-bit renamed codes
+};
 void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint64_t *keys_b,
                       uint32_t *vals_b, long n, const int *shifts, int n_shifts,
                       uint64_t **keys_out, uint32_t **vals_out,
                       const unsigned long long *pre_hist_d = nullptr /* [8][256] digit counts already known */,
-                      bool vals_iota = false /* values are 0..n-1: vals_a is not read */);
+                      bool vals_iota = false /* values are 0..n-1: vals_a is not read */,
+                      const KeyGen *kg = nullptr);
 
 // scan.cu
 void exclusive_scan_u32_to_u64(psc_context *ctx, const uint32_t *in, uint64_t *out, long n,

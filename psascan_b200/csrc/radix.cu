@@ -22,15 +22,6 @@ constexpr uint64_t ST_MASK = (1ull << 62) - 1;
 constexpr uint64_t ST_LOCAL = 1ull << 62;
 constexpr uint64_t ST_INCL = 2ull << 62;
 
-__device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t *p) {
-  uint64_t v;
-  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_relaxed_u64(uint64_t *p, uint64_t v) {
-  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-
 // ---- histogram of all digits in one read of the keys -----------------------------------
 __global__ void __launch_bounds__(512) radix_hist_kernel(const uint64_t *__restrict__ keys, long n,
                                                         ShiftList sl,
@@ -51,22 +42,21 @@ __global__ void __launch_bounds__(512) radix_hist_kernel(const uint64_t *__restr
 }
 
 // ---- one digit pass -----------------------------------------------------------------------
-// Shared memory (dynamic): stage_k[TILE] u64 | stage_v[TILE] u32 | gbase_adj[256] u32 |
-// warp_hist[WARPS][256] u32 | digit_off[256] u32 | wsum[8] u32 + tile id
-template <int THREADS, int ITEMS>
+// Shared memory (dynamic): stage_k[TILE] u64 | stage_v[TILE] u32 (PAIRS) | stage_d[TILE] u8 (KEYGEN) |
+// gbase_adj[256] u32 | warp_hist[WARPS][256] u32 | digit_off[256] u32 | wsum[8] u32 + tile id
+template <int THREADS, int ITEMS, bool PAIRS, bool KEYGEN>
 struct PassCfg {
   static constexpr int WARPS = THREADS / 32;
   static constexpr int TILE = THREADS * ITEMS;
-  static constexpr size_t SMEM = (size_t)TILE * 12 + RADIX * 4 + (size_t)WARPS * RADIX * 4 + RADIX * 4 + 64;
+  static constexpr size_t SMEM = (size_t)TILE * (8 + (PAIRS ? 4 : 0) + (KEYGEN ? 1 : 0)) + RADIX * 4 +
+                                 (size_t)WARPS * RADIX * 4 + RADIX * 4 + 64;
 };
 
-// lanes of the warp holding the same digit.  USE_MATCH: match.any (one ADU instruction, measured
-// ~60 cycles of the SM's ADU pipe per warp) else eight ballots (ALU/vote pipes; 1.55x faster per pass).
-// The ballot form is written in PTX: four instructions per digit bit (test, vote, select, and-xnor);
-// the compiler's own translation of the C++ took seven.
-template <bool USE_MATCH>
+// lanes of the warp holding the same digit: eight ballots (ALU/vote pipes) instead of match.any (one
+// ADU instruction, measured ~60 cycles of the SM's ADU pipe per warp; the ballots are 1.55x faster per
+// pass).  Written in PTX: four instructions per digit bit (test, vote, select, and-xnor); the
+// compiler's own translation of the C++ took seven.
 __device__ __forceinline__ uint32_t digit_peers(int d) {
-  if (USE_MATCH) return __match_any_sync(0xffffffffu, d);
   uint32_t peers;
   asm volatile(
       "{\n\t"
@@ -93,20 +83,26 @@ __device__ __forceinline__ uint32_t digit_peers(int d) {
 //   load -> early per-warp counts -> tile counts, digit offsets, PUBLISH local counts
 //   -> ranks (chunks of 4 items) and staging of keys AND values in shared memory
 //   -> only now the look-back (predecessors have long published) -> coalesced run writes.
-template <int THREADS, int ITEMS, int MINB, int MATCH>
+// PAIRS = false: keys only (the block sorter's packed mode keeps the text position in the low key bits).
+// KEYGEN: first pass of round 0 for 8-bit renamed codes: the keys are built from the text tile (staged
+// and renamed in shared memory) instead of being read, values are the positions themselves, and the
+// digit is any byte of the 8 symbols at the position, also one that the stored key does not keep.
+template <int THREADS, int ITEMS, int MINB, bool PAIRS, bool KEYGEN>
 __global__ void __launch_bounds__(THREADS, MINB)
     radix_pass_kernel(const uint64_t *__restrict__ kin, const uint32_t *__restrict__ vin,
                       uint64_t *__restrict__ kout, uint32_t *__restrict__ vout, long n, int shift,
                       const uint64_t *__restrict__ gscan,  // [256] exclusive global digit offsets
                       uint64_t *status,                    // [tiles][256] look-back chain
                       uint32_t *tile_counter,
-                      int pf_dist) {  // > 0: pull the tile `pf_dist` ahead into L2 (bulk prefetch)
+                      int pf_dist,  // > 0: pull the tile `pf_dist` ahead into L2 (bulk prefetch)
+                      const __grid_constant__ KeyGen kg) {
   constexpr int WARPS = THREADS / 32;
   constexpr int TILE = THREADS * ITEMS;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   uint64_t *stage_k = reinterpret_cast<uint64_t *>(smem_raw);
   uint32_t *stage_v = reinterpret_cast<uint32_t *>(stage_k + TILE);
-  uint32_t *gbase_adj = stage_v + TILE;          // [RADIX]
+  uint8_t *stage_d = reinterpret_cast<uint8_t *>(stage_v + (PAIRS ? TILE : 0));
+  uint32_t *gbase_adj = reinterpret_cast<uint32_t *>(stage_d + (KEYGEN ? TILE : 0));  // [RADIX]
   uint32_t *warp_hist = gbase_adj + RADIX;       // [WARPS][RADIX]
   uint32_t *digit_off = warp_hist + WARPS * RADIX;
   uint32_t *wsum = digit_off + RADIX;            // [8] + tile id at [8]
@@ -118,7 +114,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
   const long tile = wsum[8];
   const long tile_beg = tile * TILE;
   const int valid = (int)min((long)TILE, n - tile_beg);
-  if (pf_dist > 0 && tid == THREADS - 32) {
+  if (!KEYGEN && pf_dist > 0 && tid == THREADS - 32) {
     // tiles are handed out in order, so tile + (number of resident CTAs) is what this SM slot
     // will most likely load next: have the copy engine fetch it into L2 while this tile is processed
     const long pb = (tile + pf_dist) * TILE;
@@ -126,31 +122,97 @@ __global__ void __launch_bounds__(THREADS, MINB)
       const long cnt = min((long)TILE, n - pb);
       const uint32_t kb = (uint32_t)((cnt * 8) & ~15L), vb = (uint32_t)((cnt * 4) & ~15L);
       if (kb) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(kin + pb), "r"(kb) : "memory");
-      if (vin && vb) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(vin + pb), "r"(vb) : "memory");
+      if (PAIRS && vin && vb) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(vin + pb), "r"(vb) : "memory");
     }
   }
 
   // load: element order inside the tile is (warp, item, lane)
   uint64_t key[ITEMS];
-  uint32_t val[ITEMS];
+  uint32_t val[PAIRS ? ITEMS : 1];
+  uint8_t dgt[ITEMS];
   const int wbase = warp * (ITEMS * 32) + lane;
+  if constexpr (KEYGEN) {
+    // the tile's symbols (+8 for the last keys), renamed (initial_partial_sufsort.hpp:61-80), as bytes
+    // in the not yet used staging area
+    __shared__ uint8_t s_code[256];
+    uint32_t *cw = reinterpret_cast<uint32_t *>(stage_k);
+    for (int i = tid; i < 256; i += THREADS) s_code[i] = kg.code[i];
+    __syncthreads();
+    const uint32_t last4 = (uint32_t)kg.last * 0x01010101u;
+    auto rename4 = [&](uint32_t t4, long p, int nb) -> uint32_t {
+      uint32_t packed = (uint32_t)s_code[t4 & 255] | ((uint32_t)s_code[(t4 >> 8) & 255] << 8) |
+                        ((uint32_t)s_code[(t4 >> 16) & 255] << 16) | ((uint32_t)s_code[t4 >> 24] << 24);
+      if (__vcmpeq4(t4, last4)) {  // an occurrence of the block's last symbol: the gt_end bit decides its code
 #pragma unroll
-  for (int k = 0; k < ITEMS; ++k) {
-    int e = wbase + k * 32;
-    key[k] = (e < valid) ? kin[tile_beg + e] : ~0ull;
-  }
-  if (vin) {
+        for (int j = 0; j < 4; ++j) {
+          const long i = p + j;
+          if (((t4 >> (8 * j)) & 255) == (uint32_t)kg.last &&
+              (i == kg.m - 1 || kg.gt_end == nullptr || bit_get(kg.gt_end, i + 1)))
+            packed = (packed & ~(255u << (8 * j))) | ((uint32_t)kg.code_last_high << (8 * j));
+        }
+      }
+      if (nb < 4) packed &= (nb <= 0) ? 0u : (0xffffffffu >> (8 * (4 - nb)));
+      return packed;
+    };
+    if ((((uintptr_t)kg.text + (uintptr_t)tile_beg) & 15) == 0 && tile_beg + TILE + 8 <= kg.m) {
+      // whole tile inside the text and 16-byte aligned: one 128-bit load per thread
+      for (int q = tid; q < TILE / 16; q += THREADS) {
+        const uint4 t = __ldg(reinterpret_cast<const uint4 *>(kg.text + tile_beg) + q);
+        const long p = tile_beg + 16 * q;
+        *reinterpret_cast<uint4 *>(cw + 4 * q) =
+            make_uint4(rename4(t.x, p, 4), rename4(t.y, p + 4, 4), rename4(t.z, p + 8, 4), rename4(t.w, p + 12, 4));
+      }
+      if (tid < 2) {
+        const long p = tile_beg + TILE + 4 * tid;
+        cw[TILE / 4 + tid] = rename4(*reinterpret_cast<const uint32_t *>(kg.text + p), p, 4);
+      }
+    } else {
+      for (int w = tid; w < TILE / 4 + 2; w += THREADS) {
+        const long p = tile_beg + 4 * w;
+        uint32_t t4 = 0;
+        const int nb = (int)max(0L, min(4L, kg.m - p));
+        if (p + 8 <= kg.m) t4 = load_u32_any(kg.text + p);
+        else for (int j = 0; j < nb; ++j) t4 |= (uint32_t)kg.text[p + j] << (8 * j);
+        cw[w] = rename4(t4, p, nb);
+      }
+    }
+    __syncthreads();
 #pragma unroll
-    for (int k = 0; k < ITEMS; ++k) { int e = wbase + k * 32; val[k] = (e < valid) ? vin[tile_beg + e] : 0u; }
-  } else {  // implicit values 0..n-1 (first pass of round 0)
+    for (int k = 0; k < ITEMS; ++k) {
+      const int e = wbase + k * 32;
+      const int w = e >> 2, sh = (e & 3) * 8;
+      const uint32_t w0 = cw[w], w1 = cw[w + 1], w2 = cw[w + 2];
+      const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
+      const uint64_t be = ((uint64_t)__byte_perm(lo, 0, 0x0123) << 32) | (uint64_t)__byte_perm(hi, 0, 0x0123);
+      uint64_t kk = be >> kg.kshift;
+      if (kg.vbits) kk = (kk << kg.vbits) | (uint64_t)(tile_beg + e);
+      key[k] = (e < valid) ? kk : ~0ull;
+      dgt[k] = (e < valid) ? (uint8_t)((be >> kg.dshift) & 255) : (uint8_t)255;
+      if (PAIRS) val[k] = (uint32_t)(tile_beg + e);
+    }
+    __syncthreads();  // the codes alias the key staging area
+  } else {
 #pragma unroll
-    for (int k = 0; k < ITEMS; ++k) val[k] = (uint32_t)(tile_beg + wbase + k * 32);
+    for (int k = 0; k < ITEMS; ++k) {
+      int e = wbase + k * 32;
+      key[k] = (e < valid) ? kin[tile_beg + e] : ~0ull;
+    }
+    if constexpr (PAIRS) {
+      if (vin) {
+#pragma unroll
+        for (int k = 0; k < ITEMS; ++k) { int e = wbase + k * 32; val[k] = (e < valid) ? vin[tile_beg + e] : 0u; }
+      } else {  // implicit values 0..n-1 (first pass of round 0)
+#pragma unroll
+        for (int k = 0; k < ITEMS; ++k) val[k] = (uint32_t)(tile_beg + wbase + k * 32);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) dgt[k] = (uint8_t)((key[k] >> shift) & 255);
   }
   // early counts: per-warp digit histogram (fire-and-forget shared atomics, no dependent chain)
   uint32_t *wh = warp_hist + warp * RADIX;
-  uint8_t dgt[ITEMS];
 #pragma unroll
-  for (int k = 0; k < ITEMS; ++k) { dgt[k] = (uint8_t)((key[k] >> shift) & 255); atomicAdd(&wh[dgt[k]], 1u); }
+  for (int k = 0; k < ITEMS; ++k) atomicAdd(&wh[dgt[k]], 1u);
   __syncthreads();
   // per digit (thread = digit): tile count, exclusive scan over digits, per-warp start offsets
   uint32_t cnt = 0, incl = 0;
@@ -186,8 +248,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
     uint32_t peers[4], base[4];
     int lead[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
-      peers[j] = (c0 + j < MATCH) ? digit_peers<true>(dgt[c0 + j]) : digit_peers<false>(dgt[c0 + j]);
+    for (int j = 0; j < 4; ++j) peers[j] = digit_peers(dgt[c0 + j]);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       lead[j] = 31 - __clz(peers[j]);
@@ -198,7 +259,8 @@ __global__ void __launch_bounds__(THREADS, MINB)
     for (int j = 0; j < 4; ++j) {
       uint32_t pos = __shfl_sync(0xffffffffu, base[j], lead[j]) + __popc(peers[j] & lane_lt);
       stage_k[pos] = key[c0 + j];
-      stage_v[pos] = val[c0 + j];
+      if (PAIRS) stage_v[pos] = val[c0 + j];
+      if (KEYGEN) stage_d[pos] = dgt[c0 + j];
     }
   }
   // look back (thread = digit) while the other warps finish staging
@@ -237,38 +299,45 @@ __global__ void __launch_bounds__(THREADS, MINB)
     int i = tid + k * THREADS;
     if (i < valid) {
       uint64_t kk = stage_k[i];
-      uint32_t o = gbase_adj[(int)((kk >> shift) & 255)] + (uint32_t)i;
+      const int d = KEYGEN ? (int)stage_d[i] : (int)((kk >> shift) & 255);
+      uint32_t o = gbase_adj[d] + (uint32_t)i;
       kout[o] = kk;
-      vout[o] = stage_v[i];
+      if (PAIRS) vout[o] = stage_v[i];
     }
   }
 }
 
 typedef void (*PassFn)(const uint64_t *, const uint32_t *, uint64_t *, uint32_t *, long, int, const uint64_t *,
-                       uint64_t *, uint32_t *, int);
-struct PassVariant { const char *name; PassFn fn; int threads, tile; size_t smem; int minb; };
-#define PASS_VARIANT(T, I, B, M) \
-  { #T "x" #I "b" #B "m" #M, radix_pass_kernel<T, I, B, M>, T, PassCfg<T, I>::TILE, PassCfg<T, I>::SMEM, B }
-// first entry = default (measured best on B200: 2.17 ms per pass of 2^28 pairs = 2.97 TB/s);
-// PSC_RADIX_VARIANT selects another one for tuning runs (tools/tune_radix.py)
+                       uint64_t *, uint32_t *, int, const KeyGen);
+// fn[pairs][keygen]
+struct PassVariant { const char *name; PassFn fn[2][2]; int threads, items, minb_keys; size_t smem[2][2]; };
+#define PASS_VARIANT(T, I, B, BK)                                                                        \
+  { #T "x" #I "b" #B "k" #BK, {{radix_pass_kernel<T, I, BK, false, false>, radix_pass_kernel<T, I, BK, false, true>},   \
+                       {radix_pass_kernel<T, I, B, true, false>, radix_pass_kernel<T, I, B, true, true>}},      \
+    T, I, BK, {{PassCfg<T, I, false, false>::SMEM, PassCfg<T, I, false, true>::SMEM},                   \
+               {PassCfg<T, I, true, false>::SMEM, PassCfg<T, I, true, true>::SMEM}} }
+// first entry = default for pairs (measured best on B200: 6.5 ms per pass of 2^30 pairs = 3.98 TB/s);
+// PSC_RADIX_VARIANT / PSC_RADIX_VARIANT_K (keys only) select another one for tuning runs
+// (tools/tune_radix.py).  B = CTAs per SM the pair kernel is compiled for, BK = the keys-only kernel.
 static const PassVariant g_variants[] = {
-    PASS_VARIANT(512, 12, 2, 0), PASS_VARIANT(384, 12, 3, 0), PASS_VARIANT(512, 8, 3, 0), PASS_VARIANT(512, 16, 2, 0),
-    PASS_VARIANT(256, 12, 4, 0), PASS_VARIANT(1024, 8, 1, 0), PASS_VARIANT(512, 12, 2, 12),
-    PASS_VARIANT(256, 12, 5, 0), PASS_VARIANT(256, 8, 6, 0), PASS_VARIANT(384, 8, 4, 0), PASS_VARIANT(256, 16, 3, 0),
-    PASS_VARIANT(128, 12, 8, 0), PASS_VARIANT(256, 8, 8, 0),
+    PASS_VARIANT(512, 12, 2, 2), PASS_VARIANT(512, 12, 2, 3), PASS_VARIANT(384, 12, 3, 3), PASS_VARIANT(384, 12, 3, 4),
+    PASS_VARIANT(512, 8, 3, 3), PASS_VARIANT(512, 16, 2, 2), PASS_VARIANT(256, 12, 4, 5), PASS_VARIANT(384, 16, 2, 3),
+    PASS_VARIANT(256, 16, 3, 4), PASS_VARIANT(384, 8, 4, 4), PASS_VARIANT(256, 16, 3, 5), PASS_VARIANT(512, 16, 2, 3),
 };
-static const PassVariant &pass_variant() {
-  static int idx = -1;
-  if (idx < 0) {
-    idx = 0;
-    if (const char *e = getenv("PSC_RADIX_VARIANT")) {
-      for (size_t i = 0; i < sizeof(g_variants) / sizeof(g_variants[0]); ++i)
-        if (!strcmp(e, g_variants[i].name)) idx = (int)i;
-    }
+static const PassVariant &pass_variant(bool pairs) {
+  static int idx[2] = {-1, -1};
+  if (idx[0] < 0) {
+    idx[0] = idx[1] = 0;
+    const char *names[2] = {getenv("PSC_RADIX_VARIANT_K"), getenv("PSC_RADIX_VARIANT")};
+    for (int m = 0; m < 2; ++m)
+      for (size_t i = 0; names[m] && i < sizeof(g_variants) / sizeof(g_variants[0]); ++i)
+        if (!strcmp(names[m], g_variants[i].name)) idx[m] = (int)i;
     for (auto &v : g_variants)
-      cudaFuncSetAttribute((const void *)v.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v.smem);
+      for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 2; ++b)
+          cudaFuncSetAttribute((const void *)v.fn[a][b], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v.smem[a][b]);
   }
-  return g_variants[idx];
+  return g_variants[idx[pairs ? 1 : 0]];
 }
 
 __global__ void iota_kernel(uint32_t *v, long n) {
@@ -279,14 +348,17 @@ __global__ void iota_kernel(uint32_t *v, long n) {
 void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint64_t *keys_b,
                       uint32_t *vals_b, long n, const int *shifts, int n_shifts,
                       uint64_t **keys_out, uint32_t **vals_out, const unsigned long long *pre_hist_d,
-                      bool vals_iota) {
+                      bool vals_iota, const KeyGen *kg) {
+  const bool pairs = (vals_a != nullptr);  // keys only: the caller keeps the payload in the low key bits
   *keys_out = keys_a;
-  *vals_out = vals_a;
+  if (vals_out) *vals_out = vals_a;
   if (n <= 1 || n_shifts <= 0) {
-    if (vals_iota && n > 0) { iota_kernel<<<(unsigned)div_up(n, 256), 256, 0, ctx->stream>>>(vals_a, n); PSC_LAUNCH_CHECK(); }
+    if (kg) { set_error("radix_sort_pairs: key generation needs a digit pass"); throw CudaError{PSC_EARG}; }
+    if (pairs && vals_iota && n > 0) { iota_kernel<<<(unsigned)div_up(n, 256), 256, 0, ctx->stream>>>(vals_a, n); PSC_LAUNCH_CHECK(); }
     return;
   }
   if (n_shifts > MAX_PASSES) { set_error("radix_sort_pairs: too many digit passes"); throw CudaError{PSC_EARG}; }
+  if (kg && !pre_hist_d) { set_error("radix_sort_pairs: key generation needs the digit counts"); throw CudaError{PSC_EARG}; }
   PhaseTimer timer(ctx, &ctx->stats.ms_radix);
   ShiftList sl;
   sl.n = n_shifts;
@@ -317,28 +389,37 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
       run += h[p * RADIX + d];
     }
   }
+  if (kg) skip[0] = false;  // the first pass also creates the keys
   DevBuf<uint64_t> gscan(ctx, MAX_PASSES * RADIX);
   h2d(ctx, gscan.p, scans.data(), scans.size());
 
-  const PassVariant &pv = pass_variant();
-  long tiles = div_up(n, pv.tile);
+  const PassVariant &pv = pass_variant(pairs);
+  const int tile = pv.threads * pv.items;
+  long tiles = div_up(n, tile);
   static int pf_mult = -1;  // prefetch distance in units of resident CTAs (PSC_RADIX_PF, 0 = off)
   if (pf_mult < 0) { const char *e = getenv("PSC_RADIX_PF"); pf_mult = e ? atoi(e) : 1; }
-  const int pf_dist = pf_mult * ctx->n_sm * pv.minb;
   DevBuf<uint64_t> status(ctx, (size_t)tiles * RADIX);
   DevBuf<uint32_t> counter(ctx, 1);
   uint64_t *kin = keys_a, *kout = keys_b;
   uint32_t *vin = vals_a, *vout = vals_b;
+  KeyGen nokg;
+  memset(&nokg, 0, sizeof(nokg));
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> evs;
   for (int p = 0; p < n_shifts; ++p) {
     if (skip[p]) continue;
     status.zero();
     counter.zero();
+    const bool gen = (kg != nullptr && p == 0);
+    // CTAs per SM this launch gets: bounded by its shared memory and by what it was compiled for
+    const int resident = std::max(1, std::min((int)((227 * 1024) / (pv.smem[pairs][gen] + 1024)), pairs ? 8 : pv.minb_keys));
+    const int pf_dist = pf_mult * ctx->n_sm * resident;
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     cudaEventRecord(e0, ctx->stream);
-    pv.fn<<<(unsigned)tiles, pv.threads, pv.smem, ctx->stream>>>(
-        kin, vals_iota ? nullptr : vin, kout, vout, n, sl.s[p], gscan.p + p * RADIX, status.p, counter.p, pf_dist);
+    const bool first_iota = vals_iota;
+    pv.fn[pairs][gen]<<<(unsigned)tiles, pv.threads, pv.smem[pairs][gen], ctx->stream>>>(
+        kin, vals_iota ? nullptr : vin, kout, vout, n, sl.s[p], gscan.p + p * RADIX, status.p, counter.p, pf_dist,
+        gen ? *kg : nokg);
     vals_iota = false;
     cudaEventRecord(e1, ctx->stream);
     evs.push_back({e0, e1});
@@ -346,6 +427,7 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
     ctx->launches++;
     ctx->stats.radix_passes++;
     ctx->stats.radix_elems += n;
+    ctx->stats.radix_bytes += n * (long)((gen ? 1 : 8 + ((pairs && !first_iota) ? 4 : 0)) + 8 + (pairs ? 4 : 0));
     std::swap(kin, kout);
     std::swap(vin, vout);
   }
@@ -356,12 +438,12 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
     if (cudaEventElapsedTime(&ms, e.first, e.second) == cudaSuccess) ctx->stats.ms_radix_pass += ms;
     cudaEventDestroy(e.first); cudaEventDestroy(e.second);
   }
-  if (vals_iota) {  // every pass was skipped (all keys equal): materialise the implicit values
+  if (pairs && vals_iota) {  // every pass was skipped (all keys equal): materialise the implicit values
     iota_kernel<<<(unsigned)div_up(n, 256), 256, 0, ctx->stream>>>(vin, n);
     PSC_LAUNCH_CHECK();
   }
   *keys_out = kin;
-  *vals_out = vin;
+  if (vals_out) *vals_out = vin;
 }
 
 }  // namespace psc

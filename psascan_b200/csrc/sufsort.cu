@@ -11,6 +11,7 @@
 //   round r   only suffixes still sharing their key stay "active"; key = (group head << 32 |
 //             ISA[pos + h] + 1), sorted again, h doubles.
 #include <algorithm>
+#include <cmath>
 #include "scan.cuh"
 
 namespace psc {
@@ -104,90 +105,147 @@ __global__ void __launch_bounds__(SC_THREADS)
 }
 
 // ---- grouping after a sort ------------------------------------------------------------------
-// K[0..n) sorted keys.  head(i) = K[i] != K[i-1];  an element is "active" unless it is alone
-// in its group.  Tile aggregates: number of active elements, index+1 of the last head.
-__global__ void __launch_bounds__(SC_THREADS)
-    group_reduce_kernel(const uint64_t *__restrict__ K, long n, uint64_t *__restrict__ agg_act,
-                        uint64_t *__restrict__ agg_head) {
-  __shared__ uint64_t sm[SC_THREADS / 32 + 1];
-  const long base = (long)blockIdx.x * PD_TILE + (long)threadIdx.x * PD_ITEMS;
-  uint64_t prev = (base > 0 && base - 1 < n) ? K[base - 1] : 0;
-  uint64_t cur = base < n ? K[base] : 0;
-  uint64_t n_act = 0, last_head = 0;
-#pragma unroll
-  for (int k = 0; k < PD_ITEMS; ++k) {
-    long i = base + k;
-    uint64_t nxt = (i + 1 < n) ? K[i + 1] : 0;
-    if (i < n) {
-      bool head = (i == 0) || (cur != prev);
-      bool head_next = (i == n - 1) || (nxt != cur);
-      if (head) last_head = (uint64_t)i + 1;
-      if (!(head && head_next)) ++n_act;
-    }
-    prev = cur;
-    cur = nxt;
-  }
-  uint64_t tot_act, tot_head;
-  block_excl_sum<uint64_t>(n_act, sm, &tot_act);
-  block_excl_max<uint64_t>(last_head, sm, &tot_head);
-  if (threadIdx.x == 0) { agg_act[blockIdx.x] = tot_act; agg_head[blockIdx.x] = tot_head; }
+// K[0..n) sorted keys.  head(i) = key(i) != key(i-1); an element is "active" unless it is alone in
+// its group.  ONE independent pass per tile (no scan across tiles): writes SA (and ISA when it exists)
+// for the sorted elements and compacts the still-active ones into (keyY = SA slot of the group head,
+// valY = text position).  Nothing but K is needed to place an element:
+//   round 0 (hshift < 0): element i sits in SA slot i.
+//   later rounds: K[i] = (SA slot H of the head of the element's previous group) << hshift | new key
+//     bits, and the members of a previous group are contiguous in K, so slot(i) = H + (i - first
+//     index with the same H).
+// What a tile needs from before its first element (start of the group / previous group that element
+// belongs to) is found in K itself: 32 predecessors in one round trip, else a binary search (K is
+// sorted).  The active elements of a tile go to a range reserved with one atomicAdd: their order
+// across tiles is arbitrary, which the following sort does not care about.
+//   vbits == 0: values come from V; sa == nullptr means the sorted value array itself is the SA
+//               (round 0), only active elements are touched.
+//   vbits  > 0: "packed" round 0, K[i] = key << vbits | text position; every sa[i] is written.
+//   key0: key of text position 0 (round 0, vbits == 0): its SA slot goes to *i0_out.
+__device__ __forceinline__ long first_index_ge(const uint64_t *__restrict__ K, long hi, int shift, uint64_t want) {
+  long lo = 0;  // first idx in [0, hi] with (K[idx] >> shift) >= want, given (K[hi] >> shift) >= want
+  while (lo < hi) { long mid = (lo + hi) >> 1; if ((K[mid] >> shift) < want) lo = mid + 1; else hi = mid; }
+  return lo;
 }
 
-// Applies one round: writes SA (and ISA when it exists) for the sorted elements and compacts the
-// still-active ones into (keyY = new group head, valY = text position, posY = SA slot).
-//   pos == nullptr: element j sits in SA slot j (round 0); sa == nullptr: the sorted value
-//   array itself is the SA (round 0), only active elements are touched.
-__global__ void __launch_bounds__(SC_THREADS)
-    group_apply_kernel(const uint64_t *__restrict__ K, const uint32_t *__restrict__ V,
-                       const uint32_t *__restrict__ pos, long n,
-                       const uint64_t *__restrict__ agg_act, const uint64_t *__restrict__ agg_head,
-                       uint32_t *__restrict__ sa, uint32_t *__restrict__ isa,
-                       uint64_t *__restrict__ keyY, uint32_t *__restrict__ valY,
-                       uint32_t *__restrict__ posY, uint32_t *__restrict__ i0_out) {
-  __shared__ uint64_t sm[SC_THREADS / 32 + 1];
-  const long base = (long)blockIdx.x * PD_TILE + (long)threadIdx.x * PD_ITEMS;
-  bool head[PD_ITEMS], act[PD_ITEMS];
-  uint64_t prev = (base > 0 && base - 1 < n) ? K[base - 1] : 0;
-  uint64_t cur = base < n ? K[base] : 0;
-  uint64_t n_act = 0, last_head = 0;
-#pragma unroll
-  for (int k = 0; k < PD_ITEMS; ++k) {
-    long i = base + k;
-    uint64_t nxt = (i + 1 < n) ? K[i + 1] : 0;
-    head[k] = false;
-    act[k] = false;
-    if (i < n) {
-      head[k] = (i == 0) || (cur != prev);
-      bool head_next = (i == n - 1) || (nxt != cur);
-      if (head[k]) last_head = (uint64_t)i + 1;
-      act[k] = !(head[k] && head_next);
-      if (act[k]) ++n_act;
-    }
-    prev = cur;
-    cur = nxt;
+// Every warp works on its own GP_ITEMS * 32 consecutive elements (item k of lane l = element k * 32 + l,
+// so loads are coalesced, neighbours come from shuffles, and "the last head at or before me" is a bit
+// scan of a ballot) and needs nothing from the other warps: no shared memory, no block barrier.  (The
+// first versions -- 8 consecutive elements per thread, block-wide scans -- were bound by the load/store
+// unit, 32 sectors per warp load, and by the barrier + atomic round trips of a 2048-element tile.)
+constexpr int GP_THREADS = 256, GP_ITEMS = 8, GP_WARPS = GP_THREADS / 32;
+constexpr int GP_WCHUNK = GP_ITEMS * 32, GP_TILE = GP_THREADS * GP_ITEMS;
+
+// index+1 of the first element of the run of equal (K & mask) that ends at wbeg - 1, given that
+// K[wbeg - 1] & mask == want; all lanes of the warp must call
+__device__ __forceinline__ uint32_t run_start_before(const uint64_t *__restrict__ K, uint32_t wbeg, int shift,
+                                                     uint64_t mask, uint64_t want, int lane) {
+  const long idx = (long)wbeg - 1 - lane;
+  const uint64_t kv = idx >= 0 ? K[idx] : 0;
+  const uint32_t eq = __ballot_sync(0xffffffffu, idx >= 0 && (kv & mask) == want);
+  const int nn = (eq == 0xffffffffu) ? 32 : (__ffs(~eq) - 1);
+  uint32_t start = wbeg - nn;
+  if (nn == 32) {
+    if (lane == 0) start = (uint32_t)first_index_ge(K, (long)wbeg - 32, shift, want >> shift);
+    start = __shfl_sync(0xffffffffu, start, 0);
   }
-  uint64_t tot;
-  uint64_t act_off = block_excl_sum<uint64_t>(n_act, sm, &tot) + agg_act[blockIdx.x];
-  uint64_t hd = max(block_excl_max<uint64_t>(last_head, sm, &tot), agg_head[blockIdx.x]);
-  uint32_t hp = 0;
-  bool hp_valid = false;
+  return start + 1;
+}
+
+// MODE 0: round 0, (key, position) pairs; 1: round 0, packed keys; 2: later rounds.  Indices fit 32 bits
+// (blocks are < 2^31 symbols); keys are compared under a mask instead of being shifted.
+template <int MODE>
+__global__ void __launch_bounds__(GP_THREADS)
+    group_pass_kernel(const uint64_t *__restrict__ K, const uint32_t *__restrict__ V, uint32_t n, int vbits, int hshift,
+                      uint32_t *__restrict__ sa, uint32_t *__restrict__ isa,
+                      uint64_t *__restrict__ keyY, uint32_t *__restrict__ valY,
+                      const uint64_t *__restrict__ key0, uint32_t *__restrict__ i0_out,
+                      unsigned long long *__restrict__ total) {
+  constexpr bool later = (MODE == 2), packed = (MODE == 1);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t wbeg = (blockIdx.x * GP_WARPS + warp) * GP_WCHUNK;
+  if (wbeg >= n) return;
+  const uint64_t vmask = packed ? ((1ull << vbits) - 1ull) : 0ull;
+  const uint64_t kmask = ~vmask;                                   // the bits that make a group
+  const uint64_t omask = later ? (~0ull << hshift) : 0ull;         // the bits that name the previous group
+  uint64_t kw[GP_ITEMS];
 #pragma unroll
-  for (int k = 0; k < PD_ITEMS; ++k) {
-    long i = base + k;
-    if (i >= n) break;
-    if (head[k]) { hd = (uint64_t)i + 1; hp_valid = false; }
-    if (!hp_valid) { hp = pos ? pos[hd - 1] : (uint32_t)(hd - 1); hp_valid = true; }
-    if (!act[k] && sa == nullptr) continue;  // round 0: singletons stay where the sort put them
-    uint32_t v = V[i];
-    uint32_t slot = pos ? pos[i] : (uint32_t)i;
-    if (sa) sa[slot] = v;
-    if (isa) isa[v] = hp;
+  for (int k = 0; k < GP_ITEMS; ++k) {
+    const uint32_t i = wbeg + k * 32 + lane;
+    kw[k] = i < n ? K[i] : 0;
+  }
+  const uint64_t before = wbeg > 0 ? K[wbeg - 1] : 0;
+  const uint64_t after = (wbeg + GP_WCHUNK < n) ? K[wbeg + GP_WCHUNK] : 0;
+  const uint64_t k0 = (MODE == 0 && key0) ? *key0 : 0;
+  // flags as ballots (warp-uniform): group heads, active elements, heads of the previous groups
+  uint32_t hb[GP_ITEMS], ab[GP_ITEMS], ob[later ? GP_ITEMS : 1];
+  uint32_t w_act = 0;
+#pragma unroll
+  for (int k = 0; k < GP_ITEMS; ++k) {
+    const uint32_t i = wbeg + k * 32 + lane;
+    uint64_t prevw = __shfl_up_sync(0xffffffffu, kw[k], 1);
+    uint64_t nextw = __shfl_down_sync(0xffffffffu, kw[k], 1);
+    const uint64_t p31 = __shfl_sync(0xffffffffu, kw[k > 0 ? k - 1 : 0], 31);
+    const uint64_t n0 = __shfl_sync(0xffffffffu, kw[k < GP_ITEMS - 1 ? k + 1 : k], 0);
+    if (lane == 0) prevw = (k == 0) ? before : p31;
+    if (lane == 31) nextw = (k == GP_ITEMS - 1) ? after : n0;
+    const bool valid = i < n;
+    const uint64_t dp = kw[k] ^ prevw, dn = kw[k] ^ nextw;
+    const bool head = valid && ((i == 0) || (dp & kmask) != 0);
+    const bool head_next = (i + 1 >= n) || ((dn & kmask) != 0);
+    const bool act = valid && !(head && head_next);
+    hb[k] = __ballot_sync(0xffffffffu, head);
+    ab[k] = __ballot_sync(0xffffffffu, act);
+    if (later) ob[k] = __ballot_sync(0xffffffffu, valid && ((i == 0) || (dp & omask) != 0));
+    w_act += __popc(ab[k]);
+  }
+  // what the warp's first element needs from before it: start of its group / of its previous group
+  const uint64_t first = __shfl_sync(0xffffffffu, kw[0], 0);
+  uint32_t hd = 0, os = 1;
+  if (!(hb[0] & 1u)) hd = run_start_before(K, wbeg, packed ? vbits : 0, kmask, first & kmask, lane);
+  if (later && !(ob[0] & 1u)) os = run_start_before(K, wbeg, hshift, omask, first & omask, lane);
+  // room for the warp's active elements (their order across warps is arbitrary)
+  unsigned long long act_off = 0;
+  if (w_act) {
+    if (lane == 0) act_off = atomicAdd(total, (unsigned long long)w_act);
+    act_off = __shfl_sync(0xffffffffu, act_off, 0);
+  }
+  const bool touch_all = (MODE != 0);
+  const uint32_t lane_le = 0xffffffffu >> (31 - lane), lane_lt = lane_le >> 1;
+#pragma unroll
+  for (int k = 0; k < GP_ITEMS; ++k) {
+    const uint32_t ibase = wbeg + k * 32;
+    const uint32_t i = ibase + lane;
+    // last (previous-)group head at or before this element
+    if (MODE == 0 && ab[k] == 0 && !__any_sync(0xffffffffu, key0 && kw[k] == k0)) {
+      if (hb[k]) hd = ibase + (31 - __clz(hb[k])) + 1;  // nothing to write for these 32 elements
+      continue;
+    }
+    const uint32_t hm = hb[k] & lane_le;
+    const uint32_t my_hd = hm ? ibase + (31 - __clz(hm)) + 1 : hd;
+    if (hb[k]) hd = ibase + (31 - __clz(hb[k])) + 1;
+    uint32_t my_os = 1;
+    if (later) {
+      const uint32_t om = ob[k] & lane_le;
+      my_os = om ? ibase + (31 - __clz(om)) + 1 : os;
+      if (ob[k]) os = ibase + (31 - __clz(ob[k])) + 1;
+    }
+    const bool act = (ab[k] >> lane) & 1u;
+    const unsigned long long my_off = act_off + __popc(ab[k] & lane_lt);
+    act_off += __popc(ab[k]);
+    if (i >= n) continue;
+    const bool is_k0 = (MODE == 0) && key0 && kw[k] == k0;
+    if (!act && !touch_all && !is_k0) continue;  // round 0: singletons stay where the sort put them
+    const uint32_t v = packed ? (uint32_t)(kw[k] & vmask) : V[i];
+    // SA slots of this element and of its group's head: slot(j) = sbase + j inside the previous group
+    const uint32_t sbase = later ? (uint32_t)(kw[k] >> hshift) - (my_os - 1) : 0u;
+    const uint32_t slot = sbase + i, hp = sbase + my_hd - 1;
     if (v == 0 && i0_out) *i0_out = slot;
-    if (act[k]) {
-      keyY[act_off] = (uint64_t)hp;
-      valY[act_off] = v;
-      posY[act_off] = slot;
-      ++act_off;
+    if (!act && !touch_all) continue;
+    if (MODE != 0) sa[slot] = v;
+    if (isa) isa[v] = hp;
+    if (act) {
+      keyY[my_off] = (uint64_t)hp;
+      valY[my_off] = v;
     }
   }
 }
@@ -328,28 +386,6 @@ __global__ void __launch_bounds__(256)
   if (j < a) isa[valY[j]] = (uint32_t)keyY[j];
 }
 
-// position of text position 0 in the round-0 order: only the group of key0(0) is searched
-__global__ void __launch_bounds__(256)
-    find_i0_kernel(const uint64_t *__restrict__ K, const uint32_t *__restrict__ V, long m,
-                   const uint64_t *__restrict__ key_of_zero, uint32_t *__restrict__ i0_out) {
-  __shared__ long s_lo, s_hi;
-  if (threadIdx.x == 0) {
-    uint64_t k0 = *key_of_zero;
-    long lo = 0, hi = m;
-    while (lo < hi) { long mid = (lo + hi) >> 1; if (K[mid] < k0) lo = mid + 1; else hi = mid; }
-    s_lo = lo;
-    hi = m;
-    while (lo < hi) { long mid = (lo + hi) >> 1; if (K[mid] <= k0) lo = mid + 1; else hi = mid; }
-    s_hi = lo;
-  }
-  __syncthreads();
-  long beg = (long)blockIdx.x * 4096, end = min(beg + 4096, m);
-  beg = max(beg, s_lo);
-  end = min(end, s_hi);
-  for (long i = beg + threadIdx.x; i < end; i += blockDim.x)
-    if (V[i] == 0) *i0_out = (uint32_t)i;
-}
-
 static int bits_for(uint64_t v) { int b = 0; while (v) { ++b; v >>= 1; } return b; }
 
 // ---- host driver ------------------------------------------------------------------------------
@@ -408,13 +444,17 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
   DevBuf<uint32_t> valA(ctx, m), valB(ctx, m);
   long tiles = div_up(m, PD_TILE);
   DevBuf<unsigned long long> ghist(ctx, 8 * 256);
-  ghist.zero();
+  DevBuf<uint64_t> key_of_zero(ctx, 1);
+  DevBuf<uint32_t> i0_d(ctx, 1);
+  int shifts[8];
+  uint64_t *K; uint32_t *V;
+  int vbits = 0;  // > 0: packed round 0, sorted keys = key << vbits | text position, no value arrays
   // 8-bit codes: digit p of key(i) IS the code at i + k-1-p, so every digit histogram is the symbol
-  // histogram shifted by a few positions -- computed here instead of `passes` shared atomics per
-  // suffix in the kernel (8.2 -> 2.x ms for 2^30 random bytes)
-  const bool hist_on_host = (lut.bits == 8 && m >= 64);
-  std::vector<unsigned long long> gh;
-  if (hist_on_host) {
+  // histogram shifted by a few positions (computed here instead of `passes` shared atomics per suffix
+  // in a kernel), and the first digit pass builds its keys straight from the text (radix.cu, KEYGEN):
+  // no key array is written and read back before the sort.
+  const bool codes8 = (lut.bits == 8 && m >= 64);
+  if (codes8) {
     uint8_t head[8];
     uint32_t gw = 0xffffffffu;
     d2h(ctx, head, text_d, 8);
@@ -433,71 +473,97 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
       hc[j] = lut.code[c];
       if (c == last && (gt_end_bits_d == nullptr || ((gw >> (j + 1)) & 1u))) hc[j] = lut.code_last_high;
     }
-    gh.assign(8 * 256, 0);
-    for (int p = 0; p < passes; ++p) {
-      const int off = k - 1 - p;  // digit p covers positions [off, m + off); codes past the end are 0
+    // packed mode: the position rides in the low bits of the key (8 B per element and pass instead of
+    // 12) when all k symbols still fit above it.  (With fewer key bits -- the last symbol kept only in
+    // part, which the code supports -- the digit passes of 2^30 random bytes take 29 ms instead of 34,
+    // but 6 % of the suffixes stay tied instead of 0.1 % and the next round costs more than that.)
+    const int pbits = bits_for((uint64_t)(m - 1));
+    int kbits = std::min(64 - pbits, 8 * k);
+    // PSC_PACKED=0/1 forces the mode, PSC_PACKED_MAXBITS caps the key bits (tests: partly kept symbols on small texts)
+    const char *pe = getenv("PSC_PACKED"), *pm = getenv("PSC_PACKED_MAXBITS");
+    const int packed_env = pe ? atoi(pe) : 2;
+    if (pm && packed_env != 0) kbits = std::max(1, std::min(kbits, atoi(pm)));
+    bool packed = packed_env == 1 || (packed_env == 2 && kbits == 8 * k);
+    if (kbits < 8) packed = false;
+    if (!packed) kbits = 8 * k;
+    const int S = (kbits + 7) / 8;  // symbols looked at = digit passes
+    std::vector<unsigned long long> gh(8 * 256, 0);
+    for (int p = 0; p < S; ++p) {
+      const int off = S - 1 - p;  // digit p = symbol `off`: positions [off, m + off); codes past the end are 0
       for (int d = 0; d < 256; ++d) gh[p * 256 + d] = ch[d];
       for (int j = 0; j < off; ++j) gh[p * 256 + hc[j]]--;
       gh[p * 256 + 0] += (unsigned long long)off;
+      shifts[p] = (packed ? pbits : 0) + kbits - 8 * (S - p);  // pass 0 of a partly kept symbol: see KeyGen
     }
+    if (shifts[0] < 0) shifts[0] = 0;  // not used by the key-generating pass
     h2d(ctx, ghist.p, gh.data(), gh.size());
+    KeyGen kg;
+    memset(&kg, 0, sizeof(kg));
+    kg.text = text_d; kg.gt_end = gt_end_bits_d; kg.m = m;
+    kg.last = last; kg.code_last_high = lut.code_last_high;
+    kg.dshift = 64 - 8 * S; kg.kshift = 64 - kbits; kg.vbits = packed ? pbits : 0;
+    for (int c = 0; c < 256; ++c) kg.code[c] = (uint8_t)lut.code[c];
+    uint64_t key0 = 0;
+    for (int j = 0; j < 8; ++j) key0 = (key0 << 8) | (uint64_t)hc[j];
+    key0 >>= kg.kshift;
+    h2d(ctx, key_of_zero.p, &key0, 1);
+    if (packed) {
+      vbits = pbits;
+      radix_sort_pairs(ctx, keyA.p, nullptr, keyB.p, nullptr, m, shifts, S, &K, nullptr, ghist.p, false, &kg);
+      V = nullptr;
+    } else {
+      radix_sort_pairs(ctx, keyA.p, valA.p, keyB.p, valB.p, m, shifts, S, &K, &V, ghist.p, true, &kg);
+    }
+    k = kbits / 8;  // whole symbols compared so far
+    sync(ctx);      // kg, key0 and gh live on this stack frame
+  } else {
+    ghist.zero();
+    { KTrace kt(ctx, "init_keys"); init_keys_kernel<<<(unsigned)tiles, SC_THREADS, (size_t)(PD_TILE + k + (PD_TILE + k) / 32 + 8) * sizeof(uint16_t) + 8 * 256 * 4, ctx->stream>>>(
+        text_d, m, gt_end_bits_d, lut, passes, keyA.p, ghist.p); }
+    PSC_LAUNCH_CHECK();
+    ctx->launches++;
+    PSC_CUDA(cudaMemcpyAsync(key_of_zero.p, keyA.p, 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    for (int p = 0; p < passes; ++p) shifts[p] = 8 * p;
+    radix_sort_pairs(ctx, keyA.p, valA.p, keyB.p, valB.p, m, shifts, passes, &K, &V, ghist.p, true);
   }
-  { KTrace kt(ctx, "init_keys"); init_keys_kernel<<<(unsigned)tiles, SC_THREADS, (size_t)(PD_TILE + k + (PD_TILE + k) / 32 + 8) * sizeof(uint16_t) + 8 * 256 * 4, ctx->stream>>>(
-      text_d, m, gt_end_bits_d, lut, hist_on_host ? 0 : passes, keyA.p, ghist.p); }
-  PSC_LAUNCH_CHECK();
-  ctx->launches++;
-  DevBuf<uint64_t> key_of_zero(ctx, 1), total_d(ctx, 1);
-  DevBuf<uint32_t> i0_d(ctx, 1);
-  PSC_CUDA(cudaMemcpyAsync(key_of_zero.p, keyA.p, 8, cudaMemcpyDeviceToDevice, ctx->stream));
-
-  int shifts[8];
-  for (int p = 0; p < passes; ++p) shifts[p] = 8 * p;
-  uint64_t *K; uint32_t *V;
-  radix_sort_pairs(ctx, keyA.p, valA.p, keyB.p, valB.p, m, shifts, passes, &K, &V, ghist.p, true);
-  { KTrace kt(ctx, "find_i0"); find_i0_kernel<<<(unsigned)div_up(m, 4096), 256, 0, ctx->stream>>>(K, V, m, key_of_zero.p, i0_d.p); }
-  PSC_LAUNCH_CHECK();
-  ctx->launches++;
-
-  // the sorted position array IS the suffix array from here on; later rounds patch the slots of
+  // pairs: the sorted position array IS the suffix array from here on; later rounds patch the slots of
   // suffixes that were still tied.  The other value buffer and both key buffers become scratch.
-  const bool v_is_a = (V == valA.p);
+  // packed: the positions are still inside the keys; the first grouping pass writes them to valA.
+  const bool v_is_a = (vbits > 0) || (V == valA.p);
   res->sa = std::move(v_is_a ? valA : valB);
   DevBuf<uint32_t> &vfree = v_is_a ? valB : valA;
   uint64_t *kbuf[2] = {(K == keyA.p) ? keyB.p : keyA.p, K};  // compaction goes to kbuf[0] first
   DevBuf<uint32_t> valC;                                     // second value buffer, sized once `a` is known
   uint32_t *vbuf[2] = {vfree.p, nullptr};
-  DevBuf<uint32_t> posbuf[2];
-  uint32_t *pos = nullptr;  // round 0: identity
-  int out = 0, pout = 0;    // which (kbuf, vbuf) pair / posbuf the next compaction writes
+  int out = 0;  // which (kbuf, vbuf) pair the next compaction writes
   long a = m, h = k;
   const int hpbits = bits_for((uint64_t)(m > 1 ? m - 1 : 1)), lowb = bits_for((uint64_t)m);
   bool text_round_done = false;
+  DevBuf<unsigned long long> gp_total(ctx, 1);
+  int hshift = -1;  // round 0: SA slot = index
   for (int round = 0;; ++round) {
-    long t = div_up(a, PD_TILE);
-    DevBuf<uint64_t> agg_act(ctx, t), agg_head(ctx, t);
-    { KTrace kt(ctx, "group_reduce"); group_reduce_kernel<<<(unsigned)t, SC_THREADS, 0, ctx->stream>>>(K, a, agg_act.p, agg_head.p); }
+    long t = div_up(a, GP_TILE);
+    gp_total.zero();
+    {
+      KTrace kt(ctx, "group_pass");
+      auto fn = round > 0 ? group_pass_kernel<2> : (vbits > 0 ? group_pass_kernel<1> : group_pass_kernel<0>);
+      fn<<<(unsigned)t, GP_THREADS, 0, ctx->stream>>>(K, V, (uint32_t)a, vbits, hshift, res->sa.p, res->isa.p, kbuf[out],
+                                                      vbuf[out], key_of_zero.p, i0_d.p, gp_total.p);
+    }
     PSC_LAUNCH_CHECK();
-    { KTrace kt(ctx, "scan_aggregates"); scan_aggregates_sum_max(ctx, agg_act.p, agg_head.p, t, total_d.p); }
-    uint64_t na = 0;
-    d2h(ctx, &na, total_d.p, 1);
+    ctx->launches++;
+    unsigned long long na = 0;
+    d2h(ctx, &na, gp_total.p, 1);
     sync(ctx);
     if (round == 0 && na > 0) {
       valC.alloc(ctx, na);
       vbuf[1] = valC.p;
     }
-    posbuf[pout].alloc(ctx, na);
-    { KTrace kt(ctx, "group_apply"); group_apply_kernel<<<(unsigned)t, SC_THREADS, 0, ctx->stream>>>(
-        K, V, pos, a, agg_act.p, agg_head.p, round == 0 ? nullptr : res->sa.p, res->isa.p, kbuf[out], vbuf[out],
-        posbuf[pout].p, i0_d.p); }
-    PSC_LAUNCH_CHECK();
-    ctx->launches += 2;
     ctx->stats.doubling_rounds++;
     if (na == 0) break;
     a = (long)na;
     uint64_t *KY = kbuf[out];
     uint32_t *VY = vbuf[out];
-    pos = posbuf[pout].p;
-    pout ^= 1;
     int nsh = 0;
     const int k1 = (64 - hpbits) / lut.bits;
     if (!text_round_done && k1 >= 1) {
@@ -507,6 +573,7 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
                                                                                 lut, h, k1); }
       PSC_LAUNCH_CHECK();
       for (int b = 0; b < k1 * lut.bits + hpbits; b += 8) shifts[nsh++] = b;
+      hshift = k1 * lut.bits;
       h += k1;
     } else {
       text_round_done = true;
@@ -536,6 +603,7 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
       PSC_LAUNCH_CHECK();
       for (int b = 0; b < lowb; b += 8) shifts[nsh++] = b;
       for (int b = 0; b < hpbits; b += 8) shifts[nsh++] = 32 + b;
+      hshift = 32;
       h *= 2;
     }
     ctx->launches++;

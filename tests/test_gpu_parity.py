@@ -52,6 +52,25 @@ def test_golden_sa5_bit_exact(ctx, name, gen, kw, n, sa5):
     assert np.array_equal(ctx.construct_sa(text, max_block=1024), sa5)
 
 
+@pytest.mark.parametrize("env", [dict(PSC_PACKED="0"), dict(PSC_PACKED="1"), dict(PSC_PACKED="1", PSC_PACKED_MAXBITS="13"),
+                                 dict(PSC_PACKED="1", PSC_PACKED_MAXBITS="9"), dict(PSC_PACKED="1", PSC_PACKED_MAXBITS="21")],
+                         ids=["pairs_keygen", "packed", "packed13", "packed9", "packed21"])
+@pytest.mark.parametrize("sigma", [255, 200, 129])
+def test_sort_modes_8bit_codes(ctx, monkeypatch, env, sigma):
+    """Round 0 for 8-bit renamed codes: keys built from the text inside the first digit pass, as
+    (key, position) pairs or packed into one word, also with a partly kept last symbol (few key bits:
+    many ties go on to the later rounds).  Single block, and blocks with a tail (renaming by gt_end)."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    rng = np.random.default_rng(sigma)
+    text = rng.integers(0, sigma, size=70001, dtype=np.uint8)
+    text[5000:5600] = text[100:700]          # some long repeats: ties past round 0
+    text[-300:] = text[40000:40300]
+    want = O.sa(text)
+    assert np.array_equal(decode_sa5(ctx.construct_sa(text)), want)
+    assert np.array_equal(decode_sa5(ctx.construct_sa(text, max_block=30000)), want)
+
+
 def test_sentinel_255_rejected(ctx):
     import psascan_b200 as P
     text = textgen.dna(5000).copy()

@@ -1,17 +1,23 @@
-"""Times one radix digit pass (24 B/pair of algorithmic traffic) for every kernel variant."""
+"""Times one radix digit pass for every kernel variant: (key64, val32) pairs (24 B per element of
+algorithmic traffic) or, with --keys, keys only (16 B)."""
 import os, subprocess, sys, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-VARIANTS = sys.argv[2:] or ["512x12b2m0", "512x12b2m4", "512x12b2m6", "512x12b2m8", "512x12b2m12", "384x12b3m0",
-                            "384x12b3m6", "384x12b3m8", "512x8b3m0", "512x8b3m4", "512x16b2m8", "512x16b2m10",
-                            "256x12b4m6", "256x16b3m8", "1024x8b1m4", "1024x12b1m8"]
-n = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 28
+args = [a for a in sys.argv[1:] if a != "--keys"]
+keys = "--keys" in sys.argv
+VARIANTS = args[1:] or ["512x12b2k2", "512x12b2k3", "384x12b3k3", "384x12b3k4", "512x8b3k3", "512x16b2k2", "256x12b4k5",
+                        "384x16b2k3", "256x16b3k4", "384x8b4k4", "256x16b3k5", "512x16b2k3"]
+n = int(args[0]) if args else 1 << 28
 code = ("import sys; sys.path.insert(0, %r); import psascan_b200 as P; c = P.Context(0); "
         "ms = c.bench_radix_pass(%d, 8); print('%%.4f' %% ms)" % (ROOT, n))
 for v in VARIANTS:
-    env = dict(os.environ, PSC_RADIX_VARIANT=v)
+    env = dict(os.environ)
+    env["PSC_RADIX_VARIANT_K" if keys else "PSC_RADIX_VARIANT"] = v
+    if keys:
+        env["PSC_BENCH_KEYS_ONLY"] = "1"
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True)
     try:
         ms = float(r.stdout.strip().splitlines()[-1])
-        print(json.dumps({"variant": v, "n": n, "ms_per_pass": ms, "GBps": 24.0 * n / ms / 1e6}))
+        print(json.dumps({"variant": v, "keys_only": keys, "n": n, "ms_per_pass": ms,
+                          "GBps": (16.0 if keys else 24.0) * n / ms / 1e6}))
     except Exception:
         print(json.dumps({"variant": v, "error": (r.stderr or r.stdout)[-300:]}))
