@@ -78,6 +78,35 @@ __device__ __forceinline__ uint32_t digit_peers(int d) {
   return peers;
 }
 
+// Decoupled look-back of one digit: sum of the counts of the tiles before `tile`.  Predecessors are
+// read LB at a time (independent loads, one L2 round trip per batch).  Measured per pass of 2^28 pairs:
+// LB = 1: 1.78 ms, 2: 1.67, 4: 1.58, 8: 1.73, 16: 2.03, 32: 2.26 -- most walks end within a few tiles
+// and every status load that is not needed competes with the tile data for the L2.
+template <int LB>
+__device__ __forceinline__ uint64_t look_back(const uint64_t *status, long tile, int tid, int nap) {
+  uint64_t excl = 0;
+  long t = tile - 1;
+  bool done = false;
+  while (!done) {
+    uint64_t v[LB];
+#pragma unroll
+    for (int j = 0; j < LB; ++j) v[j] = (t - j >= 0) ? ld_relaxed_u64(status + (size_t)(t - j) * RADIX + tid) : ST_INCL;
+    int used = 0;
+#pragma unroll
+    for (int j = 0; j < LB; ++j) {
+      uint64_t f = v[j] & ~ST_MASK;
+      if (!done && used == j && f != 0) {
+        excl += v[j] & ST_MASK;
+        used = j + 1;
+        if (f == ST_INCL) done = true;
+      }
+    }
+    t -= used;  // an unpublished status stops the batch; it is read again
+    if (used == 0 && nap > 0) __nanosleep(nap);
+  }
+  return excl;
+}
+
 // Order of work in a tile (ncu stall samples of the previous version: 15 % of the time was spent
 // waiting in the look-back, 25 % on the initial loads):
 //   load -> early per-warp counts -> tile counts, digit offsets, PUBLISH local counts
@@ -95,6 +124,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
                       uint64_t *status,                    // [tiles][256] look-back chain
                       uint32_t *tile_counter,
                       int pf_dist,  // > 0: pull the tile `pf_dist` ahead into L2 (bulk prefetch)
+                      int lb_mode,  // look-back tuning (PSC_RADIX_LB): batch size and back-off, 0 = default
                       const __grid_constant__ KeyGen kg) {
   constexpr int WARPS = THREADS / 32;
   constexpr int TILE = THREADS * ITEMS;
@@ -267,26 +297,15 @@ __global__ void __launch_bounds__(THREADS, MINB)
   if (tid < RADIX) {
     uint64_t excl = 0;
     if (tile > 0) {
-      // predecessors are read LB at a time (independent loads, one L2 round trip): measured
-      // depth of the walk was 14 tiles = 14 dependent round trips with one load per step
-      constexpr int LB = 8;
-      long t = tile - 1;
-      bool done = false;
-      while (!done) {
-        uint64_t v[LB];
-#pragma unroll
-        for (int j = 0; j < LB; ++j) v[j] = (t - j >= 0) ? ld_relaxed_u64(status + (size_t)(t - j) * RADIX + tid) : ST_INCL;
-        int used = 0;
-#pragma unroll
-        for (int j = 0; j < LB; ++j) {
-          uint64_t f = v[j] & ~ST_MASK;
-          if (!done && used == j && f != 0) {
-            excl += v[j] & ST_MASK;
-            used = j + 1;
-            if (f == ST_INCL) done = true;
-          }
-        }
-        t -= used;  // an unpublished status stops the batch; it is read again
+      const int nap = (lb_mode >> 3) * 64;  // ns to sleep when a batch made no progress
+      switch (lb_mode & 7) {
+        case 1: excl = look_back<8>(status, tile, tid, nap); break;
+        case 2: excl = look_back<16>(status, tile, tid, nap); break;
+        case 3: excl = look_back<2>(status, tile, tid, nap); break;
+        case 4: excl = look_back<3>(status, tile, tid, nap); break;
+        case 5: excl = look_back<5>(status, tile, tid, nap); break;
+        case 6: excl = look_back<6>(status, tile, tid, nap); break;
+        default: excl = look_back<4>(status, tile, tid, nap); break;
       }
       uint32_t cnt_valid = cnt - ((tid == 255) ? (uint32_t)(TILE - valid) : 0u);
       st_relaxed_u64(status + (size_t)tile * RADIX + tid, ST_INCL | (excl + cnt_valid));
@@ -308,7 +327,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 }
 
 typedef void (*PassFn)(const uint64_t *, const uint32_t *, uint64_t *, uint32_t *, long, int, const uint64_t *,
-                       uint64_t *, uint32_t *, int, const KeyGen);
+                       uint64_t *, uint32_t *, int, int, const KeyGen);
 // fn[pairs][keygen]
 struct PassVariant { const char *name; PassFn fn[2][2]; int threads, items, minb_keys; size_t smem[2][2]; };
 #define PASS_VARIANT(T, I, B, BK)                                                                        \
@@ -396,8 +415,11 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
   const PassVariant &pv = pass_variant(pairs);
   const int tile = pv.threads * pv.items;
   long tiles = div_up(n, tile);
-  static int pf_mult = -1;  // prefetch distance in units of resident CTAs (PSC_RADIX_PF, 0 = off)
-  if (pf_mult < 0) { const char *e = getenv("PSC_RADIX_PF"); pf_mult = e ? atoi(e) : 1; }
+  static int pf_mult = -1, lb_mode = 0;  // prefetch distance in units of resident CTAs (PSC_RADIX_PF, 0 = off)
+  if (pf_mult < 0) {
+    const char *e = getenv("PSC_RADIX_PF"); pf_mult = e ? atoi(e) : 1;
+    e = getenv("PSC_RADIX_LB"); lb_mode = e ? atoi(e) : 0;
+  }
   DevBuf<uint64_t> status(ctx, (size_t)tiles * RADIX);
   DevBuf<uint32_t> counter(ctx, 1);
   uint64_t *kin = keys_a, *kout = keys_b;
@@ -419,7 +441,7 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
     const bool first_iota = vals_iota;
     pv.fn[pairs][gen]<<<(unsigned)tiles, pv.threads, pv.smem[pairs][gen], ctx->stream>>>(
         kin, vals_iota ? nullptr : vin, kout, vout, n, sl.s[p], gscan.p + p * RADIX, status.p, counter.p, pf_dist,
-        gen ? *kg : nokg);
+        lb_mode, gen ? *kg : nokg);
     vals_iota = false;
     cudaEventRecord(e1, ctx->stream);
     evs.push_back({e0, e1});
