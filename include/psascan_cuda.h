@@ -152,6 +152,8 @@ typedef struct psc_stats {
   long n_blocks, lf_steps, radix_passes, radix_elems, doubling_rounds, walkers, kernel_launches;
   long radix_bytes; /* algorithmic bytes of the digit passes: 12 in + 12 out per (key64, val32) pair, 8 + 8 for a
                      * keys-only pass, 1 in for a pass that builds its keys from the text */
+  long radix_keygen_bytes; /* the share of radix_bytes moved by key-building passes ... */
+  double ms_radix_keygen;  /* ... and their share of ms_radix_pass */
 } psc_stats;
 int psc_get_stats(psc_context *ctx, psc_stats *out);
 

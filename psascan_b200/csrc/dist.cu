@@ -338,7 +338,7 @@ void construct_sa_pipelined(psc_context *ctx, const uint8_t *text_d, long n, lon
   const psc_stats &a = aux->stats;
   ctx->stats.ms_gt_end += a.ms_gt_end; ctx->stats.ms_sort += a.ms_sort; ctx->stats.ms_radix += a.ms_radix;
   ctx->stats.ms_bwt += a.ms_bwt; ctx->stats.ms_radix_pass += a.ms_radix_pass;
-  ctx->stats.radix_passes += a.radix_passes; ctx->stats.radix_elems += a.radix_elems; ctx->stats.radix_bytes += a.radix_bytes;
+  ctx->stats.radix_passes += a.radix_passes; ctx->stats.radix_elems += a.radix_elems; ctx->stats.radix_bytes += a.radix_bytes; ctx->stats.radix_keygen_bytes += a.radix_keygen_bytes; ctx->stats.ms_radix_keygen += a.ms_radix_keygen;
   ctx->stats.doubling_rounds += a.doubling_rounds;
   ctx->stats.kernel_launches = ctx->launches + aux->launches;
   for (auto &r : aux->trace_rows) ctx->trace_rows.push_back(r);

@@ -427,6 +427,7 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
   KeyGen nokg;
   memset(&nokg, 0, sizeof(nokg));
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> evs;
+  std::vector<bool> ev_gen;
   for (int p = 0; p < n_shifts; ++p) {
     if (skip[p]) continue;
     status.zero();
@@ -445,20 +446,26 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
     vals_iota = false;
     cudaEventRecord(e1, ctx->stream);
     evs.push_back({e0, e1});
+    ev_gen.push_back(gen);
     PSC_LAUNCH_CHECK();
     ctx->launches++;
     ctx->stats.radix_passes++;
     ctx->stats.radix_elems += n;
-    ctx->stats.radix_bytes += n * (long)((gen ? 1 : 8 + ((pairs && !first_iota) ? 4 : 0)) + 8 + (pairs ? 4 : 0));
+    const long pass_bytes = n * (long)((gen ? 1 : 8 + ((pairs && !first_iota) ? 4 : 0)) + 8 + (pairs ? 4 : 0));
+    ctx->stats.radix_bytes += pass_bytes;
+    if (gen) ctx->stats.radix_keygen_bytes += pass_bytes;
     std::swap(kin, kout);
     std::swap(vin, vout);
   }
   // the host vector `scans` must outlive the async copy
   sync(ctx);
-  for (auto &e : evs) {
+  for (size_t q = 0; q < evs.size(); ++q) {
     float ms = 0;
-    if (cudaEventElapsedTime(&ms, e.first, e.second) == cudaSuccess) ctx->stats.ms_radix_pass += ms;
-    cudaEventDestroy(e.first); cudaEventDestroy(e.second);
+    if (cudaEventElapsedTime(&ms, evs[q].first, evs[q].second) == cudaSuccess) {
+      ctx->stats.ms_radix_pass += ms;
+      if (ev_gen[q]) ctx->stats.ms_radix_keygen += ms;
+    }
+    cudaEventDestroy(evs[q].first); cudaEventDestroy(evs[q].second);
   }
   if (pairs && vals_iota) {  // every pass was skipped (all keys equal): materialise the implicit values
     iota_kernel<<<(unsigned)div_up(n, 256), 256, 0, ctx->stream>>>(vin, n);

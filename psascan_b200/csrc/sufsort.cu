@@ -182,16 +182,19 @@ __global__ void __launch_bounds__(GP_THREADS)
 #pragma unroll
   for (int k = 0; k < GP_ITEMS; ++k) {
     const uint32_t i = wbeg + k * 32 + lane;
+    // neighbours: shuffles inside the item; lanes 0 and 31 re-read theirs (an L1 hit: the warp has just
+    // loaded those lines), which is cheaper than two more 64-bit shuffles per item
     uint64_t prevw = __shfl_up_sync(0xffffffffu, kw[k], 1);
     uint64_t nextw = __shfl_down_sync(0xffffffffu, kw[k], 1);
-    const uint64_t p31 = __shfl_sync(0xffffffffu, kw[k > 0 ? k - 1 : 0], 31);
-    const uint64_t n0 = __shfl_sync(0xffffffffu, kw[k < GP_ITEMS - 1 ? k + 1 : k], 0);
-    if (lane == 0) prevw = (k == 0) ? before : p31;
-    if (lane == 31) nextw = (k == GP_ITEMS - 1) ? after : n0;
+    if (lane == 0) prevw = (k == 0) ? before : ((i - 1 < n) ? K[i - 1] : 0);
+    if (lane == 31) nextw = (k == GP_ITEMS - 1) ? after : ((i + 1 < n) ? K[i + 1] : 0);
     const bool valid = i < n;
-    const uint64_t dp = kw[k] ^ prevw, dn = kw[k] ^ nextw;
-    const bool head = valid && ((i == 0) || (dp & kmask) != 0);
-    const bool head_next = (i + 1 >= n) || ((dn & kmask) != 0);
+    bool dpk, dnk;  // differs from the previous / next element in the group bits
+    if (MODE == 0) { dpk = kw[k] != prevw; dnk = kw[k] != nextw; }
+    else { dpk = ((kw[k] ^ prevw) & kmask) != 0; dnk = ((kw[k] ^ nextw) & kmask) != 0; }
+    const uint64_t dp = kw[k] ^ prevw;
+    const bool head = valid && ((i == 0) || dpk);
+    const bool head_next = (i + 1 >= n) || dnk;
     const bool act = valid && !(head && head_next);
     hb[k] = __ballot_sync(0xffffffffu, head);
     ab[k] = __ballot_sync(0xffffffffu, act);
