@@ -201,19 +201,18 @@ def main():
             dev_text.copy_(host_text)
 
     def step_dev():
-        if sharded:
-            pdist.construct_sa_distributed(ctx, dev_text.data_ptr(), n, dev_out.data_ptr(), max_block)
+        if sharded:   # every rank ends up with its n/world slice of the SA (merge sharded by output range)
+            pdist.construct_sa_slices(ctx, dev_text.data_ptr(), n, dev_out.data_ptr(), max_block)
         else:
             ctx.construct_sa_ptr(dev_text.data_ptr(), n, dev_out.data_ptr(), max_block, device=True)
         return ctx.stats()
 
     def step_e2e():
-        if sharded:   # host text -> HBM on every rank, sharded construction, SA back to rank 0's host
+        if sharded:   # host text -> HBM on every rank, sharded construction, every rank's slice back to its host
             dev_text.copy_(host_text, non_blocking=True)
             torch.cuda.synchronize()
-            pdist.construct_sa_distributed(ctx, dev_text.data_ptr(), n, dev_out.data_ptr(), max_block)
-            if rank == 0:
-                host_out.copy_(dev_out, non_blocking=True)
+            _, ln, _ = pdist.construct_sa_slices(ctx, dev_text.data_ptr(), n, dev_out.data_ptr(), max_block)
+            host_out[:5 * ln].copy_(dev_out[:5 * ln], non_blocking=True)
             torch.cuda.synchronize()
         else:
             ctx.construct_sa_ptr(host_text.data_ptr(), n, host_out.data_ptr(), max_block, device=False)
@@ -298,11 +297,13 @@ def main():
                 "steps": a.steps, "warmup": a.warmup, "ms_per_step": dev_ms / a.steps, "higher_is_better": True,
                 "scaling": "strong" if sharded else "weak", "vs_baseline": None,
                 "dtype": "u8 text, u64 keys, u32 ranks", "data": "synthetic",
-                "config": dict(config, parallelism=("block sorts per GPU + sharded tail walk + NCCL all-reduce of gap counts"
+                "config": dict(config, parallelism=("block sorts per GPU + sharded tail walk + NCCL all-reduce of gap counts + merge sharded by "
+                                                    "output range (one all-to-all per level); every rank keeps n/N of the SA"
                                                     if sharded else "replicas" if world > 1 else "single GPU"),
                                max_block=max_block),
                 "clocks": clocks, "wall_ms_per_step": wall_ms / a.steps,
-                "e2e": {"value": e2e, "unit": "MB/s", "h2d_bytes_per_step": n, "d2h_bytes_per_step": 5 * n,
+                "e2e": {"value": e2e, "unit": "MB/s", "h2d_bytes_per_step": n * world if sharded else n,
+                        "d2h_bytes_per_step": 5 * n,
                         "ms_per_step": e2e_ms / a.steps},
                 "gpu_launches": s["kernel_launches"] * a.steps, "roofline": roof,
                 "phases_ms": {k: s[k] for k in s if k.startswith("ms_")},

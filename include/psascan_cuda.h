@@ -136,13 +136,33 @@ int psc_construct_sa_d(psc_context *ctx, const uint8_t *text_d, long n, long max
  * are delegated to the caller (NCCL through torch.distributed in psascan_b200/dist.py):
  *   fn(user, PSC_COLL_BCAST, buf_d, bytes, root)           broadcast buf_d from rank `root`
  *   fn(user, PSC_COLL_ALLREDUCE_SUM_U32, buf_d, bytes, 0)  element-wise uint32 sum over all ranks
- * fn must return 0 after the operation has COMPLETED on the device.  Every rank passes the whole
- * text and receives the whole suffix array. */
+ *   fn(user, PSC_COLL_ALLTOALLV, args, bytes, 0)           args = psc_alltoallv_args* (HOST memory): rank r
+ *                                                          sends send_bytes[h] consecutive bytes of send_d to every
+ *                                                          rank h (in rank order) and receives recv_bytes[h] from
+ *                                                          it into recv_d (in rank order); bytes = total received
+ * fn must return 0 after the operation has COMPLETED on the device.  Every rank passes the whole text.
+ * The merge (merge.hpp:54-180) is sharded by output range: after each level a rank holds an n/world
+ * slice of the merged sequence and fetches the slice of the previous level it needs with one all-to-all.
+ *   psc_construct_sa_dist_d        every rank receives the whole suffix array (slices broadcast at the end)
+ *   psc_construct_sa_dist_slice_d  every rank keeps its slice: entries [*slice_beg, *slice_beg + *slice_len) of
+ *                                  the SA as 5-byte values in out_slice_sa5_d, which must hold
+ *                                  psc_dist_slice_capacity(n, world) entries */
 #define PSC_COLL_BCAST 1
 #define PSC_COLL_ALLREDUCE_SUM_U32 2
+#define PSC_COLL_ALLTOALLV 3
+typedef struct psc_alltoallv_args {
+  const void *send_d;
+  void *recv_d;
+  const size_t *send_bytes; /* [world] */
+  const size_t *recv_bytes; /* [world] */
+} psc_alltoallv_args;
 typedef int (*psc_collective_fn)(void *user, int op, void *buf_d, size_t bytes, int root);
 int psc_construct_sa_dist_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
                             uint8_t *out_sa5_d, int rank, int world, psc_collective_fn fn, void *user);
+int psc_construct_sa_dist_slice_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
+                                  uint8_t *out_slice_sa5_d, long *slice_beg, long *slice_len, int rank, int world,
+                                  psc_collective_fn fn, void *user);
+long psc_dist_slice_capacity(long n, int world);
 
 /* per-phase device time (ms, CUDA events) and counters of the last psc_construct_sa* call */
 typedef struct psc_stats {

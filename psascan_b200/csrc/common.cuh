@@ -324,6 +324,14 @@ void walk_tail_range(psc_context *ctx, const psc_rank *rk, long i0, uint8_t last
 void merge_level(psc_context *ctx, const uint32_t *sa_d, const uint32_t *gap_d, long m, long beg,
                  const uint32_t *right_lo, const uint8_t *right_hi, long right_len,
                  uint32_t *out_lo, uint8_t *out_hi);
+// pieces of one level for callers that own only a range of the output slots (dist.cu): E = exclusive scan
+// of the gap array (m + 1 entries); merge_bounds: number of block suffixes in slots below each given slot
+void merge_gap_scan(psc_context *ctx, const uint32_t *gap_d, long m, uint64_t *E_d);
+void merge_bounds(psc_context *ctx, const uint64_t *E_d, long m, const uint64_t *slots, int nq, uint64_t *before);
+void sa_slice_to_planes(psc_context *ctx, const uint32_t *sa_d, long count, long beg, uint32_t *out_lo, uint8_t *out_hi);
+void merge_level_range(psc_context *ctx, const uint32_t *sa_d, const uint64_t *E_d, long m, long beg,
+                       const uint32_t *right_lo, const uint8_t *right_hi, long r_base, long q_beg, long q_end,
+                       uint32_t *out_lo, uint8_t *out_hi);
 void pack_sa5(psc_context *ctx, const uint32_t *lo, const uint8_t *hi, long n, uint8_t *out5);
 void pack_sa5_from_sa(psc_context *ctx, const uint32_t *sa, long n, long beg, uint8_t *out5);
 void unpack_sa5(psc_context *ctx, const uint8_t *in5, long n, uint32_t *lo, uint8_t *hi);

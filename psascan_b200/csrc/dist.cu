@@ -5,7 +5,11 @@
 //   phase 2  blocks right to left: the owner broadcasts SA, BWT and gt_begin bits of the block;
 //            every rank builds the rank structure, walks ITS contiguous share of the tail
 //            (compute_gap.hpp:68-69 splits the tail over threads the same way), and the per-GPU
-//            gap counts and gt bits are summed over NCCL; the merge level is replicated.
+//            gap counts and gt bits are summed over NCCL.  The merge is sharded by OUTPUT range:
+//            after every level rank g holds slots [g*L/G, (g+1)*L/G) of the merged sequence (L = its
+//            length so far); the entries of the previous level it needs form one contiguous range,
+//            known to every rank from the scanned gap array alone, and arrive by one all-to-all.
+//            Nothing of size n lives on a GPU except the text: planes and output are n/G per rank.
 // Collectives are delegated to the caller through psc_collective_fn (torch.distributed in
 // psascan_b200/dist.py, NCCL over NVLink); the library synchronises its stream around them.
 #include <algorithm>
@@ -85,8 +89,23 @@ static void coll(psc_context *ctx, psc_collective_fn fn, void *user, int op, voi
   }
 }
 
+// first output slot of rank g when `len` slots are shared out: equal shares rounded up to a multiple of 4
+// (the 40-bit writer packs 4 entries into 5 aligned words)
+static long share_begin(long g, long len, int world) {
+  long per = (div_up(len, (long)world) + 3) / 4 * 4;
+  return std::min(len, per * g);
+}
+long share_begin_public(long g, long len, int world) { return share_begin(g, len, world); }
+static size_t overlap(long a0, long a1, long b0, long b1) {
+  long lo = std::max(a0, b0), hi = std::min(a1, b1);
+  return hi > lo ? (size_t)(hi - lo) : 0;
+}
+
+// gather == true: out_sa5_d[5n] receives the whole SA on every rank (slices broadcast at the end);
+// else out_sa5_d receives this rank's slice only: entries [*slice_beg, *slice_beg + *slice_len).
 void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max_block, uint8_t *out_sa5_d,
-                       int rank, int world, psc_collective_fn fn, void *user) {
+                       int rank, int world, psc_collective_fn fn, void *user, bool gather, long *slice_beg,
+                       long *slice_len) {
   memset(&ctx->stats, 0, sizeof(ctx->stats));
   ctx->launches = 0;
   if (n == 0) return;
@@ -111,9 +130,13 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
   DevBuf<uint32_t> Ga(ctx, gwords), Gb(ctx, gwords);
   Ga.zero(); Gb.zero();
   uint32_t *gt_cur = Ga.p, *gt_new = Gb.p;
-  DevBuf<uint32_t> Mlo[2];
-  DevBuf<uint8_t> Mhi[2];
-  for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); if (n > (1L << 32)) Mhi[k].alloc(ctx, n);  /* high bytes only above 4 GiB */ }
+  // my share of the merged sequence (double buffered) and what arrives from the other ranks per level
+  const bool hi_plane = n > (1L << 32);  // high bytes only above 4 GiB
+  const long cap = share_begin(1, n, world) + 16;
+  DevBuf<uint32_t> Mlo[2], Rlo;
+  DevBuf<uint8_t> Mhi[2], Rhi;
+  for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, cap); if (hi_plane) Mhi[k].alloc(ctx, cap); }
+  if (world > 1) { Rlo.alloc(ctx, cap); if (hi_plane) Rhi.alloc(ctx, cap); }
   DevBuf<BlockMeta> meta_d(ctx, 1);
   int cur = 0;
   long right_len = 0;
@@ -180,14 +203,61 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
       ctx->launches += 2;
     }
     int nxt = 1 - cur;
-    merge_level(ctx, sa_p, gap.p, m, beg, Mlo[cur].p, Mhi[cur].p, right_len, Mlo[nxt].p, Mhi[nxt].p);
+    {
+      const long R = right_len, L = R + m;
+      const long a = share_begin(rank, L, world), b = share_begin(rank + 1, L, world);
+      if (R == 0) {
+        sa_slice_to_planes(ctx, sa_p + a, b - a, beg, Mlo[nxt].p, Mhi[nxt].p);
+      } else {
+        DevBuf<uint64_t> E(ctx, m + 1);
+        merge_gap_scan(ctx, gap.p, m, E.p);
+        if (world == 1) {
+          merge_level_range(ctx, sa_p, E.p, m, beg, Mlo[cur].p, Mhi[cur].p, 0, 0, L, Mlo[nxt].p, Mhi[nxt].p);
+        } else {
+          // output slot Q[g] is preceded by cnt[g] block suffixes, hence by ra[g] = Q[g] - cnt[g] entries of the
+          // right side: rank g needs entries [ra[g], ra[g+1]) of the previous level, held in shares P[.]
+          std::vector<uint64_t> Q(world + 1), cnt(world + 1);
+          std::vector<long> ra(world + 1), P(world + 1);
+          for (int g = 0; g <= world; ++g) { Q[g] = (uint64_t)share_begin(g, L, world); P[g] = share_begin(g, R, world); }
+          merge_bounds(ctx, E.p, m, Q.data(), world + 1, cnt.data());
+          for (int g = 0; g <= world; ++g) ra[g] = (long)(Q[g] - cnt[g]);
+          std::vector<size_t> sb(world), rb(world), sb4(world), rb4(world);
+          size_t rtot = 0;
+          for (int h = 0; h < world; ++h) {
+            sb[h] = overlap(P[rank], P[rank + 1], ra[h], ra[h + 1]);
+            rb[h] = overlap(P[h], P[h + 1], ra[rank], ra[rank + 1]);
+            sb4[h] = sb[h] * 4; rb4[h] = rb[h] * 4;
+            rtot += rb[h];
+          }
+          if ((long)rtot != ra[rank + 1] - ra[rank] || (long)rtot > cap) { set_error("sharded merge: inconsistent exchange plan"); throw CudaError{PSC_EARG}; }
+          psc_alltoallv_args x{Mlo[cur].p, Rlo.p, sb4.data(), rb4.data()};
+          coll(ctx, fn, user, PSC_COLL_ALLTOALLV, &x, rtot * 4, 0);
+          if (hi_plane) {
+            psc_alltoallv_args y{Mhi[cur].p, Rhi.p, sb.data(), rb.data()};
+            coll(ctx, fn, user, PSC_COLL_ALLTOALLV, &y, rtot, 0);
+          }
+          merge_level_range(ctx, sa_p, E.p, m, beg, Rlo.p, Rhi.p, ra[rank], a, b, Mlo[nxt].p, Mhi[nxt].p);
+        }
+      }
+    }
     cur = nxt;
     right_len += m;
     std::swap(gt_cur, gt_new);
     sync(ctx);
     mine[id].reset();
   }
-  pack_sa5(ctx, Mlo[cur].p, Mhi[cur].p, n, out_sa5_d);
+  {
+    const long a = share_begin(rank, n, world), b = share_begin(rank + 1, n, world);
+    if (slice_beg) *slice_beg = a;
+    if (slice_len) *slice_len = b - a;
+    pack_sa5(ctx, Mlo[cur].p, Mhi[cur].p, b - a, gather ? out_sa5_d + 5 * a : out_sa5_d);
+    if (gather && world > 1) {
+      for (int h = 0; h < world; ++h) {
+        const long ha = share_begin(h, n, world), hb = share_begin(h + 1, n, world);
+        if (hb > ha) coll(ctx, fn, user, PSC_COLL_BCAST, out_sa5_d + 5 * ha, (size_t)(hb - ha) * 5, h);
+      }
+    }
+  }
   sync(ctx);
   ctx->stats.kernel_launches = ctx->launches;
 }
@@ -347,20 +417,41 @@ void construct_sa_pipelined(psc_context *ctx, const uint8_t *text_d, long n, lon
 
 }  // namespace psc
 
-extern "C" int psc_construct_sa_dist_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
-                                       uint8_t *out_sa5_d, int rank, int world, psc_collective_fn fn,
-                                       void *user) {
+static int dist_entry(psc_context *ctx, const uint8_t *text_d, long n, long max_block, uint8_t *out_sa5_d, int rank,
+                      int world, psc_collective_fn fn, void *user, bool gather, long *slice_beg, long *slice_len,
+                      const char *who) {
   try {
     if (!ctx || n < 0 || (n > 0 && (!text_d || !out_sa5_d)) || world < 1 || rank < 0 || rank >= world ||
         max_block <= 0 || (world > 1 && !fn)) {
-      psc::set_error("bad argument: psc_construct_sa_dist_d");
+      psc::set_error("bad argument: %s", who);
       return PSC_EARG;
     }
     PSC_CUDA(cudaSetDevice(ctx->device));
-    psc::construct_sa_dist(ctx, text_d, n, max_block, out_sa5_d, rank, world, fn, user);
+    if (slice_beg) *slice_beg = 0;
+    if (slice_len) *slice_len = 0;
+    psc::construct_sa_dist(ctx, text_d, n, max_block, out_sa5_d, rank, world, fn, user, gather, slice_beg, slice_len);
     psc::trace_report(ctx);
     return PSC_OK;
   } catch (const psc::CudaError &e) {
     return e.code;
   }
+}
+
+extern "C" int psc_construct_sa_dist_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
+                                       uint8_t *out_sa5_d, int rank, int world, psc_collective_fn fn,
+                                       void *user) {
+  return dist_entry(ctx, text_d, n, max_block, out_sa5_d, rank, world, fn, user, true, nullptr, nullptr,
+                    "psc_construct_sa_dist_d");
+}
+
+extern "C" int psc_construct_sa_dist_slice_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
+                                             uint8_t *out_slice_sa5_d, long *slice_beg, long *slice_len, int rank,
+                                             int world, psc_collective_fn fn, void *user) {
+  if (!slice_beg || !slice_len) { psc::set_error("bad argument: psc_construct_sa_dist_slice_d"); return PSC_EARG; }
+  return dist_entry(ctx, text_d, n, max_block, out_slice_sa5_d, rank, world, fn, user, false, slice_beg, slice_len,
+                    "psc_construct_sa_dist_slice_d");
+}
+
+extern "C" long psc_dist_slice_capacity(long n, int world) {
+  return world < 1 || n < 0 ? 0 : psc::share_begin_public(1, n, world);
 }

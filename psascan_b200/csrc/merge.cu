@@ -22,10 +22,11 @@ constexpr int MG_TILE = SC_THREADS * MG_ITEMS;  // outputs per block
 // order), and a prefix popcount turns every slot into either "block suffix u0+k" or "entry
 // q-(u0+k) of the right side".  O(1) work per slot, all global accesses coalesced.
 __global__ void __launch_bounds__(256)
-    merge_tile_start_kernel(const uint64_t *__restrict__ E, long m, long ntiles, uint32_t *__restrict__ tile_u0) {
+    merge_tile_start_kernel(const uint64_t *__restrict__ E, long m, long ntiles, uint64_t q_base,
+                            uint32_t *__restrict__ tile_u0) {
   long tile = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (tile >= ntiles) return;
-  const uint64_t q0 = (uint64_t)tile * MG_TILE;
+  const uint64_t q0 = q_base + (uint64_t)tile * MG_TILE;
   long lo = 0, hi = m;  // largest u in [0, m] with u + E[u] <= q0
   while (lo < hi) {
     long mid = (lo + hi + 1) >> 1;
@@ -39,12 +40,13 @@ template <bool HI>
 __global__ void __launch_bounds__(SC_THREADS)
     merge_level_kernel(const uint32_t *__restrict__ sa, const uint64_t *__restrict__ E,
                        const uint32_t *__restrict__ tile_u0, long m, uint64_t beg, const uint32_t *__restrict__ right_lo,
-                       const uint8_t *__restrict__ right_hi, long total,
+                       const uint8_t *__restrict__ right_hi, long q_base, long total, long r_base,
                        uint32_t *__restrict__ out_lo, uint8_t *__restrict__ out_hi) {
+  // output slots [q_base, total) of the level go to out[0 ..); right_lo/hi[0] is entry r_base of the right side
   constexpr int WORDS = MG_TILE / 32;
   __shared__ uint32_t flags[WORDS];
   __shared__ uint32_t before[WORDS];
-  const long q0 = (long)blockIdx.x * MG_TILE;
+  const long q0 = q_base + (long)blockIdx.x * MG_TILE;
   if (threadIdx.x < WORDS) flags[threadIdx.x] = 0;
   const long u0 = (long)tile_u0[blockIdx.x];
   __syncthreads();
@@ -79,12 +81,12 @@ __global__ void __launch_bounds__(SC_THREADS)
     if ((word >> (i & 31)) & 1u) {
       v = beg + sa[u0 + nb];
     } else {
-      uint64_t r = (uint64_t)q - (uint64_t)(u0 + nb);  // block suffixes before slot q: u0 + nb
+      uint64_t r = (uint64_t)q - (uint64_t)(u0 + nb) - (uint64_t)r_base;  // block suffixes before slot q: u0 + nb
       v = (uint64_t)right_lo[r];
       if (HI) v |= (uint64_t)right_hi[r] << 32;
     }
-    out_lo[q] = (uint32_t)v;
-    if (HI) out_hi[q] = (uint8_t)(v >> 32);
+    out_lo[q - q_base] = (uint32_t)v;
+    if (HI) out_hi[q - q_base] = (uint8_t)(v >> 32);
   }
 }
 
@@ -98,36 +100,76 @@ __global__ void __launch_bounds__(256)
   if (hi) hi[i] = (uint8_t)(v >> 32);
 }
 
-void merge_level(psc_context *ctx, const uint32_t *sa_d, const uint32_t *gap_d, long m, long beg,
-                 const uint32_t *right_lo, const uint8_t *right_hi, long right_len,
-                 uint32_t *out_lo, uint8_t *out_hi) {
-  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
-  long total = m + right_len;
-  if (total == 0) return;
-  if (right_len == 0) {
-    { KTrace kt(ctx, "sa_to_planes"); sa_to_planes_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(sa_d, m, (uint64_t)beg, out_lo, out_hi); }
-    PSC_LAUNCH_CHECK();
-    ctx->launches++;
-    return;
+// number of block suffixes in output slots below q[j] (= the run slot q[j] lies in), for a few slots
+__global__ void merge_bounds_kernel(const uint64_t *__restrict__ E, long m, const uint64_t *__restrict__ q, int nq,
+                                    uint64_t *__restrict__ out) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nq) return;
+  long lo = 0, hi = m;  // largest u in [0, m] with u + E[u] <= q[j]
+  while (lo < hi) {
+    long mid = (lo + hi + 1) >> 1;
+    if ((uint64_t)mid + E[mid] <= q[j]) lo = mid; else hi = mid - 1;
   }
-  DevBuf<uint64_t> E(ctx, m + 1);
-  { KTrace kt(ctx, "gap_scan"); exclusive_scan_u32_to_u64(ctx, gap_d, E.p, m + 1, nullptr); }
-  const long ntiles = div_up(total, MG_TILE);
+  out[j] = (uint64_t)lo;
+}
+
+void merge_gap_scan(psc_context *ctx, const uint32_t *gap_d, long m, uint64_t *E_d) {
+  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
+  KTrace kt(ctx, "gap_scan");
+  exclusive_scan_u32_to_u64(ctx, gap_d, E_d, m + 1, nullptr);
+}
+
+void merge_bounds(psc_context *ctx, const uint64_t *E_d, long m, const uint64_t *slots, int nq, uint64_t *before) {
+  DevBuf<uint64_t> q(ctx, nq), out(ctx, nq);
+  h2d(ctx, q.p, slots, nq);
+  merge_bounds_kernel<<<div_up(nq, 64), 64, 0, ctx->stream>>>(E_d, m, q.p, nq, out.p);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+  d2h(ctx, before, out.p, nq);
+  sync(ctx);
+}
+
+void sa_slice_to_planes(psc_context *ctx, const uint32_t *sa_d, long count, long beg, uint32_t *out_lo, uint8_t *out_hi) {
+  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
+  if (count <= 0) return;
+  { KTrace kt(ctx, "sa_to_planes"); sa_to_planes_kernel<<<(unsigned)div_up(count, 256), 256, 0, ctx->stream>>>(sa_d, count, (uint64_t)beg, out_lo, out_hi); }
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+}
+
+// output slots [q_beg, q_end) of one level; right_lo/hi[0] = entry r_base of the right side
+void merge_level_range(psc_context *ctx, const uint32_t *sa_d, const uint64_t *E_d, long m, long beg,
+                       const uint32_t *right_lo, const uint8_t *right_hi, long r_base, long q_beg, long q_end,
+                       uint32_t *out_lo, uint8_t *out_hi) {
+  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
+  if (q_end <= q_beg) return;
+  const long ntiles = div_up(q_end - q_beg, MG_TILE);
   DevBuf<uint32_t> tile_u0(ctx, ntiles);
-  { KTrace kt(ctx, "merge_tile_start"); merge_tile_start_kernel<<<(unsigned)div_up(ntiles, 256), 256, 0, ctx->stream>>>(E.p, m, ntiles, tile_u0.p); }
+  { KTrace kt(ctx, "merge_tile_start"); merge_tile_start_kernel<<<(unsigned)div_up(ntiles, 256), 256, 0, ctx->stream>>>(E_d, m, ntiles, (uint64_t)q_beg, tile_u0.p); }
   PSC_LAUNCH_CHECK();
   ctx->launches++;
   {
     KTrace kt(ctx, "merge_level");
     if (out_hi)
       merge_level_kernel<true><<<(unsigned)ntiles, SC_THREADS, 0, ctx->stream>>>(
-          sa_d, E.p, tile_u0.p, m, (uint64_t)beg, right_lo, right_hi, total, out_lo, out_hi);
+          sa_d, E_d, tile_u0.p, m, (uint64_t)beg, right_lo, right_hi, q_beg, q_end, r_base, out_lo, out_hi);
     else
       merge_level_kernel<false><<<(unsigned)ntiles, SC_THREADS, 0, ctx->stream>>>(
-          sa_d, E.p, tile_u0.p, m, (uint64_t)beg, right_lo, right_hi, total, out_lo, out_hi);
+          sa_d, E_d, tile_u0.p, m, (uint64_t)beg, right_lo, right_hi, q_beg, q_end, r_base, out_lo, out_hi);
   }
   PSC_LAUNCH_CHECK();
   ctx->launches++;
+}
+
+void merge_level(psc_context *ctx, const uint32_t *sa_d, const uint32_t *gap_d, long m, long beg,
+                 const uint32_t *right_lo, const uint8_t *right_hi, long right_len,
+                 uint32_t *out_lo, uint8_t *out_hi) {
+  long total = m + right_len;
+  if (total == 0) return;
+  if (right_len == 0) { sa_slice_to_planes(ctx, sa_d, m, beg, out_lo, out_hi); return; }
+  DevBuf<uint64_t> E(ctx, m + 1);
+  merge_gap_scan(ctx, gap_d, m, E.p);
+  merge_level_range(ctx, sa_d, E.p, m, beg, right_lo, right_hi, 0, 0, total, out_lo, out_hi);
 }
 
 // ---- 40-bit writer: 4 entries = 20 bytes = 5 aligned words per thread --------------------------

@@ -2,13 +2,27 @@
 csrc/dist.cu with its collectives served by NCCL (or gloo on CPU buffers in the host-logic tests).
 
 Sharding: block sorts on separate GPUs, the tail walk of every block split into
-`world` contiguous shares, per-GPU gap counts summed (all-reduce over NVLink), gt bits OR-ed.
+`world` contiguous shares, per-GPU gap counts summed (all-reduce over NVLink), gt bits OR-ed, and the
+merge sharded by output range: every rank keeps n/world entries of the merged sequence and fetches the
+range of the previous level it needs with one all-to-all.
 """
 import ctypes as C
 import numpy as np
 
-COLL_BCAST, COLL_ALLREDUCE_SUM_U32 = 1, 2
+COLL_BCAST, COLL_ALLREDUCE_SUM_U32, COLL_ALLTOALLV = 1, 2, 3
 COLLECTIVE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_int)
+
+
+class AllToAllVArgs(C.Structure):
+    """psc_alltoallv_args (include/psascan_cuda.h): host struct the library passes for COLL_ALLTOALLV"""
+    _fields_ = [("send_d", C.c_void_p), ("recv_d", C.c_void_p),
+                ("send_bytes", C.POINTER(C.c_size_t)), ("recv_bytes", C.POINTER(C.c_size_t))]
+
+
+def share_begin(g, length, world):
+    """first output slot of rank g when `length` slots are shared out (csrc/dist.cu share_begin)"""
+    per = (-(-length // world) + 3) // 4 * 4
+    return min(length, per * g)
 
 
 def block_bounds(n, max_block):
@@ -50,7 +64,8 @@ def make_collective(cuda=True, group=None):
     """the psc_collective_fn served by torch.distributed; returns (ctypes callback, call counter)"""
     import torch
     import torch.distributed as dist
-    counter = {"bcast": 0, "allreduce": 0, "bytes": 0}
+    counter = {"bcast": 0, "allreduce": 0, "alltoall": 0, "bytes": 0}
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
 
     def fn(user, op, buf, nbytes, root):
         try:
@@ -63,6 +78,15 @@ def make_collective(cuda=True, group=None):
                 t = tensor_from_pointer(buf, nbytes, "i4", cuda)
                 dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
                 counter["allreduce"] += 1
+            elif op == COLL_ALLTOALLV:
+                a = C.cast(buf, C.POINTER(AllToAllVArgs)).contents
+                sb = [int(a.send_bytes[h]) for h in range(world)]
+                rb = [int(a.recv_bytes[h]) for h in range(world)]
+                empty = torch.empty(0, dtype=torch.uint8, device="cuda" if cuda else "cpu")
+                src = tensor_from_pointer(a.send_d, sum(sb), "u1", cuda) if sum(sb) else empty
+                dst = tensor_from_pointer(a.recv_d, sum(rb), "u1", cuda) if sum(rb) else empty
+                dist.all_to_all_single(dst, src, output_split_sizes=rb, input_split_sizes=sb, group=group)
+                counter["alltoall"] += 1
             else:
                 return 1
             counter["bytes"] += nbytes
@@ -76,15 +100,39 @@ def make_collective(cuda=True, group=None):
     return COLLECTIVE_FN(fn), counter
 
 
-def construct_sa_distributed(ctx, text_dev_ptr, n, out_dev_ptr, max_block, rank=None, world=None):
-    """SPMD call: every rank passes the whole text (device pointer) and gets the whole SA."""
+def _rank_world(rank, world):
     import torch.distributed as dist
     if world is None:
         world = dist.get_world_size() if dist.is_initialized() else 1
         rank = dist.get_rank() if dist.is_initialized() else 0
+    return rank, world
+
+
+def construct_sa_distributed(ctx, text_dev_ptr, n, out_dev_ptr, max_block, rank=None, world=None):
+    """SPMD call: every rank passes the whole text (device pointer) and gets the whole SA."""
+    rank, world = _rank_world(rank, world)
     cb, counter = make_collective(cuda=True)
     f = ctx.lib.psc_construct_sa_dist_d
     rc = f(ctx.h, C.c_void_p(text_dev_ptr), C.c_long(n), C.c_long(max_block), C.c_void_p(out_dev_ptr),
            C.c_int(rank), C.c_int(world), cb, None)
     ctx._chk(rc)
     return counter
+
+
+def slice_capacity(ctx, n, world):
+    """entries the slice buffer of construct_sa_slices must hold"""
+    ctx.lib.psc_dist_slice_capacity.restype = C.c_long
+    return int(ctx.lib.psc_dist_slice_capacity(C.c_long(n), C.c_int(world)))
+
+
+def construct_sa_slices(ctx, text_dev_ptr, n, out_slice_dev_ptr, max_block, rank=None, world=None):
+    """SPMD call: every rank passes the whole text and keeps its slice of the SA (5-byte entries
+    [beg, beg + length) in out_slice_dev_ptr); returns (beg, length, collective counters)."""
+    rank, world = _rank_world(rank, world)
+    cb, counter = make_collective(cuda=True)
+    beg, length = C.c_long(0), C.c_long(0)
+    rc = ctx.lib.psc_construct_sa_dist_slice_d(ctx.h, C.c_void_p(text_dev_ptr), C.c_long(n), C.c_long(max_block),
+                                               C.c_void_p(out_slice_dev_ptr), C.byref(beg), C.byref(length),
+                                               C.c_int(rank), C.c_int(world), cb, None)
+    ctx._chk(rc)
+    return beg.value, length.value, counter

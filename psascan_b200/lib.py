@@ -13,6 +13,7 @@ EXPORTS = [
     "psc_merge_bwt", "psc_split_gap", "psc_construct_sa", "psc_construct_sa_d", "psc_get_stats",
     "psc_bench_random_sectors", "psc_bench_radix_pass", "psc_device_alloc", "psc_device_free",
     "psc_pinned_alloc", "psc_pinned_free", "psc_copy_h2d", "psc_copy_d2h", "psc_device_info", "psc_construct_sa_dist_d",
+    "psc_construct_sa_dist_slice_d", "psc_dist_slice_capacity",
 ]
 
 

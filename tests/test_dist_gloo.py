@@ -35,6 +35,16 @@ def _worker(rank, world, port, q):
         assert cb(None, D.COLL_BCAST, b.ctypes.data, b.nbytes, 1) == 0
         assert (b == np.arange(77, dtype=np.uint8)).all()
         assert counter["allreduce"] == 2 and counter["bcast"] == 1
+        # all-to-all with ragged shares: rank r sends (h + 1) * (r + 2) bytes of value 10 * r + h to rank h
+        sb = [(h + 1) * (rank + 2) for h in range(world)]
+        rb = [(rank + 1) * (h + 2) for h in range(world)]
+        src = np.concatenate([np.full(sb[h], 10 * rank + h, dtype=np.uint8) for h in range(world)])
+        dst = np.zeros(sum(rb), dtype=np.uint8)
+        sb_c, rb_c = (C.c_size_t * world)(*sb), (C.c_size_t * world)(*rb)
+        args = D.AllToAllVArgs(src.ctypes.data, dst.ctypes.data, sb_c, rb_c)
+        assert cb(None, D.COLL_ALLTOALLV, C.addressof(args), dst.nbytes, 0) == 0
+        assert np.array_equal(dst, np.concatenate([np.full(rb[h], 10 * h + rank, dtype=np.uint8) for h in range(world)]))
+        assert counter["alltoall"] == 1
 
         # 2. the distributed schedule with the oracle as the engine
         for gen, kw, n, mb in [("dna", dict(seed=3), 5000, 1300), ("periodic", dict(period=37, sigma=3), 4000, 999),
@@ -55,6 +65,8 @@ def _worker(rank, world, port, q):
             # phase 2
             gt_cur = z.copy()
             pieces = []
+            shard = np.zeros(0, dtype=np.int64)   # my slice of the merged sequence (csrc/dist.cu, sharded merge)
+            right_len = 0
             for bid in range(B - 1, -1, -1):
                 beg, end = blocks[bid]
                 m, t = end - beg, n - end
@@ -88,9 +100,43 @@ def _worker(rank, world, port, q):
                 gt_new[beg + 1:end + 1] |= gtb[beg + 1:end + 1]
                 pieces.append((beg, m, psa, gap))
                 gt_cur = gt_new
+                # one level of the merge sharded by output range, with the exchange plan of csrc/dist.cu
+                R, L = right_len, right_len + m
+                a, b = D.share_begin(rank, L, world), D.share_begin(rank + 1, L, world)
+                if R == 0:
+                    shard = beg + psa[a:b].astype(np.int64)
+                else:
+                    E = np.concatenate([[0], np.cumsum(gap)])[:m + 1]          # exclusive scan
+                    A = np.arange(m + 1) + E                                     # run u starts at slot A[u]
+                    Q = [D.share_begin(g, L, world) for g in range(world + 1)]
+                    cnt = [int(np.searchsorted(A, q, side="right")) - 1 for q in Q]
+                    ra = [q - c for q, c in zip(Q, cnt)]
+                    P = [D.share_begin(g, R, world) for g in range(world + 1)]
+                    ov = lambda a0, a1, b0, b1: max(0, min(a1, b1) - max(a0, b0))
+                    sb = [8 * ov(P[rank], P[rank + 1], ra[h], ra[h + 1]) for h in range(world)]
+                    rb = [8 * ov(P[h], P[h + 1], ra[rank], ra[rank + 1]) for h in range(world)]
+                    assert ra[0] == 0 and ra[world] == R and sum(sb) == 8 * len(shard)
+                    recv = np.zeros(sum(rb) // 8, dtype=np.int64)
+                    src = np.ascontiguousarray(shard)
+                    args = D.AllToAllVArgs(src.ctypes.data, recv.ctypes.data, (C.c_size_t * world)(*sb),
+                                           (C.c_size_t * world)(*rb))
+                    assert cb(None, D.COLL_ALLTOALLV, C.addressof(args), recv.nbytes, 0) == 0
+                    out = np.empty(b - a, dtype=np.int64)
+                    is_blk = np.zeros(b - a, dtype=bool)
+                    slot = np.arange(m) + E[1:m + 1]                             # block suffix u sits at u + E[u+1]
+                    sel = (slot >= a) & (slot < b)
+                    is_blk[slot[sel] - a] = True
+                    out[is_blk] = beg + psa[sel].astype(np.int64)
+                    assert (~is_blk).sum() == len(recv)
+                    out[~is_blk] = recv
+                    shard = out
+                right_len = L
             pieces.sort()
             sa = O.merge([p[0] for p in pieces], [p[1] for p in pieces], [p[2] for p in pieces], [p[3] for p in pieces])
             assert np.array_equal(sa, ref), (gen, rank)
+            parts = [None] * world
+            dist.all_gather_object(parts, shard)
+            assert np.array_equal(np.concatenate(parts), ref), (gen, rank, "sharded merge")
         q.put((rank, "ok"))
     except Exception as e:
         import traceback

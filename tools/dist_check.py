@@ -43,6 +43,24 @@ for name, text, sa5, mbs in cases:
             st = ctx.stats()
             print(f"{name} n={n} max_block={mb} world={world} ok={bool(flag.item())} {dt*1e3:.1f} ms "
                   f"walk {st['ms_walk']:.2f} ms sort {st['ms_sort']:.2f} ms coll {cnt}", flush=True)
+# the slice API: every rank keeps its share of the SA; gathered here only for the comparison
+for name, text, sa5, mbs in cases[-3:]:
+    n = len(text)
+    d_text = torch.from_numpy(text).cuda()
+    capn = D.slice_capacity(ctx, n, world)
+    d_slice = torch.zeros(5 * capn, dtype=torch.uint8, device="cuda")
+    if sa5 is None:
+        sa5 = ctx.construct_sa(text, max_block=mbs[0])
+    beg, ln, cnt = D.construct_sa_slices(ctx, d_text.data_ptr(), n, d_slice.data_ptr(), mbs[0])
+    good = bool(np.array_equal(d_slice[:5 * ln].cpu().numpy(), sa5[5 * beg:5 * (beg + ln)]))
+    lens = [None] * world
+    dist.all_gather_object(lens, (beg, ln))
+    good = good and sum(x[1] for x in lens) == n and all(lens[i][0] + lens[i][1] == lens[i + 1][0] for i in range(world - 1))
+    flag = torch.tensor([1 if good else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    ok = ok and bool(flag.item())
+    if rank == 0:
+        print(f"slices {name} n={n} max_block={mbs[0]} world={world} ok={bool(flag.item())} shares {lens} coll {cnt}", flush=True)
 ctx.close()
 dist.destroy_process_group()
 sys.exit(0 if ok else 1)
