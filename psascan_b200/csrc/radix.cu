@@ -83,26 +83,33 @@ __device__ __forceinline__ uint32_t digit_peers(int d) {
 // LB = 1: 1.78 ms, 2: 1.67, 4: 1.58, 8: 1.73, 16: 2.03, 32: 2.26 -- most walks end within a few tiles
 // and every status load that is not needed competes with the tile data for the L2.
 template <int LB>
-__device__ __forceinline__ uint64_t look_back(const uint64_t *status, long tile, int tid, int nap) {
-  uint64_t excl = 0;
-  long t = tile - 1;
-  bool done = false;
+__device__ __forceinline__ void look_back_consume(const uint64_t (&v)[LB], uint64_t &excl, long &t, bool &done) {
+  int used = 0;
+#pragma unroll
+  for (int j = 0; j < LB; ++j) {
+    uint64_t f = v[j] & ~ST_MASK;
+    if (!done && used == j && f != 0) {
+      excl += v[j] & ST_MASK;
+      used = j + 1;
+      if (f == ST_INCL) done = true;
+    }
+  }
+  t -= used;  // an unpublished status stops the batch; it is read again
+}
+template <int LB>
+__device__ __forceinline__ void look_back_load(const uint64_t *status, long t, int tid, uint64_t (&v)[LB]) {
+#pragma unroll
+  for (int j = 0; j < LB; ++j) v[j] = (t - j >= 0) ? ld_relaxed_u64(status + (size_t)(t - j) * RADIX + tid) : ST_INCL;
+}
+// continues the walk at tile t (the caller may already have consumed a prefetched batch)
+template <int LB>
+__device__ __forceinline__ uint64_t look_back(const uint64_t *status, long t, int tid, int nap, uint64_t excl, bool done) {
   while (!done) {
     uint64_t v[LB];
-#pragma unroll
-    for (int j = 0; j < LB; ++j) v[j] = (t - j >= 0) ? ld_relaxed_u64(status + (size_t)(t - j) * RADIX + tid) : ST_INCL;
-    int used = 0;
-#pragma unroll
-    for (int j = 0; j < LB; ++j) {
-      uint64_t f = v[j] & ~ST_MASK;
-      if (!done && used == j && f != 0) {
-        excl += v[j] & ST_MASK;
-        used = j + 1;
-        if (f == ST_INCL) done = true;
-      }
-    }
-    t -= used;  // an unpublished status stops the batch; it is read again
-    if (used == 0 && nap > 0) __nanosleep(nap);
+    look_back_load<LB>(status, t, tid, v);
+    const long t0 = t;
+    look_back_consume<LB>(v, excl, t, done);
+    if (t == t0 && nap > 0) __nanosleep(nap);
   }
   return excl;
 }
@@ -116,7 +123,7 @@ __device__ __forceinline__ uint64_t look_back(const uint64_t *status, long tile,
 // KEYGEN: first pass of round 0 for 8-bit renamed codes: the keys are built from the text tile (staged
 // and renamed in shared memory) instead of being read, values are the positions themselves, and the
 // digit is any byte of the 8 symbols at the position, also one that the stored key does not keep.
-template <int THREADS, int ITEMS, int MINB, bool PAIRS, bool KEYGEN>
+template <int THREADS, int ITEMS, int MINB, bool PAIRS, bool KEYGEN, int CH = 4>
 __global__ void __launch_bounds__(THREADS, MINB)
     radix_pass_kernel(const uint64_t *__restrict__ kin, const uint32_t *__restrict__ vin,
                       uint64_t *__restrict__ kout, uint32_t *__restrict__ vout, long n, int shift,
@@ -273,20 +280,26 @@ __global__ void __launch_bounds__(THREADS, MINB)
   // ranks: peers of each item, then one shared atomic per distinct digit (issued back to back;
   // same-address atomics of one warp retire in issue order, which keeps the sort stable)
   const uint32_t lane_lt = (1u << lane) - 1;
+  // (lb_mode & 64): the first look-back batch is loaded half way through the ranking, so its L2 round trip
+  // overlaps with work instead of being waited for at the end
+  constexpr int PF_AT = (ITEMS / 2) / CH * CH;
+  uint64_t pre[4];
+  const bool pre_on = (lb_mode & 64) && tid < RADIX && tile > 0;
 #pragma unroll
-  for (int c0 = 0; c0 < ITEMS; c0 += 4) {
-    uint32_t peers[4], base[4];
-    int lead[4];
+  for (int c0 = 0; c0 < ITEMS; c0 += CH) {
+    if (c0 == PF_AT && pre_on) look_back_load<4>(status, tile - 1, tid, pre);
+    uint32_t peers[CH], base[CH];
+    int lead[CH];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) peers[j] = digit_peers(dgt[c0 + j]);
+    for (int j = 0; j < CH; ++j) peers[j] = digit_peers(dgt[c0 + j]);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < CH; ++j) {
       lead[j] = 31 - __clz(peers[j]);
       base[j] = 0;
       if (lane == lead[j]) base[j] = atomicAdd(&wh[dgt[c0 + j]], (uint32_t)__popc(peers[j]));
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < CH; ++j) {
       uint32_t pos = __shfl_sync(0xffffffffu, base[j], lead[j]) + __popc(peers[j] & lane_lt);
       stage_k[pos] = key[c0 + j];
       if (PAIRS) stage_v[pos] = val[c0 + j];
@@ -297,15 +310,18 @@ __global__ void __launch_bounds__(THREADS, MINB)
   if (tid < RADIX) {
     uint64_t excl = 0;
     if (tile > 0) {
-      const int nap = (lb_mode >> 3) * 64;  // ns to sleep when a batch made no progress
+      const int nap = ((lb_mode >> 3) & 7) * 64;  // ns to sleep when a batch made no progress
+      long t = tile - 1;
+      bool done = false;
+      if (pre_on) look_back_consume<4>(pre, excl, t, done);
       switch (lb_mode & 7) {
-        case 1: excl = look_back<8>(status, tile, tid, nap); break;
-        case 2: excl = look_back<16>(status, tile, tid, nap); break;
-        case 3: excl = look_back<2>(status, tile, tid, nap); break;
-        case 4: excl = look_back<3>(status, tile, tid, nap); break;
-        case 5: excl = look_back<5>(status, tile, tid, nap); break;
-        case 6: excl = look_back<6>(status, tile, tid, nap); break;
-        default: excl = look_back<4>(status, tile, tid, nap); break;
+        case 1: excl = look_back<8>(status, t, tid, nap, excl, done); break;
+        case 2: excl = look_back<16>(status, t, tid, nap, excl, done); break;
+        case 3: excl = look_back<2>(status, t, tid, nap, excl, done); break;
+        case 4: excl = look_back<3>(status, t, tid, nap, excl, done); break;
+        case 5: excl = look_back<5>(status, t, tid, nap, excl, done); break;
+        case 6: excl = look_back<6>(status, t, tid, nap, excl, done); break;
+        default: excl = look_back<4>(status, t, tid, nap, excl, done); break;
       }
       uint32_t cnt_valid = cnt - ((tid == 255) ? (uint32_t)(TILE - valid) : 0u);
       st_relaxed_u64(status + (size_t)tile * RADIX + tid, ST_INCL | (excl + cnt_valid));
@@ -330,24 +346,34 @@ typedef void (*PassFn)(const uint64_t *, const uint32_t *, uint64_t *, uint32_t 
                        uint64_t *, uint32_t *, int, int, const KeyGen);
 // fn[pairs][keygen]
 struct PassVariant { const char *name; PassFn fn[2][2]; int threads, items, minb_keys; size_t smem[2][2]; };
-#define PASS_VARIANT(T, I, B, BK)                                                                        \
-  { #T "x" #I "b" #B "k" #BK, {{radix_pass_kernel<T, I, BK, false, false>, radix_pass_kernel<T, I, BK, false, true>},   \
-                       {radix_pass_kernel<T, I, B, true, false>, radix_pass_kernel<T, I, B, true, true>}},      \
+#define PASS_VARIANT(T, I, B, BK) PASS_VARIANT_C(T, I, B, BK, 4)
+#define PASS_VARIANT_C(T, I, B, BK, CH)                                                                        \
+  { #T "x" #I "b" #B "k" #BK "c" #CH, {{radix_pass_kernel<T, I, BK, false, false, CH>, radix_pass_kernel<T, I, BK, false, true, CH>},   \
+                       {radix_pass_kernel<T, I, B, true, false, CH>, radix_pass_kernel<T, I, B, true, true, CH>}},      \
     T, I, BK, {{PassCfg<T, I, false, false>::SMEM, PassCfg<T, I, false, true>::SMEM},                   \
                {PassCfg<T, I, true, false>::SMEM, PassCfg<T, I, true, true>::SMEM}} }
-// first entry = default for pairs (measured best on B200: 6.5 ms per pass of 2^30 pairs = 3.98 TB/s);
-// PSC_RADIX_VARIANT / PSC_RADIX_VARIANT_K (keys only) select another one for tuning runs
-// (tools/tune_radix.py).  B = CTAs per SM the pair kernel is compiled for, BK = the keys-only kernel.
+// PSC_RADIX_VARIANT / PSC_RADIX_VARIANT_K (keys only) select a variant for tuning runs (tools/tune_radix.py);
+// the defaults are named in pass_variant().  B = CTAs per SM the pair kernel is compiled for, BK = the
+// keys-only kernel, C = items ranked per step of the ranking loop (1: 1.46 ms, 2: 1.47, 4: 1.51, 6: 1.72,
+// 12: 1.93 ms per 2^28 pairs -- more items in flight only cost registers).
 static const PassVariant g_variants[] = {
     PASS_VARIANT(512, 12, 2, 2), PASS_VARIANT(512, 12, 2, 3), PASS_VARIANT(384, 12, 3, 3), PASS_VARIANT(384, 12, 3, 4),
     PASS_VARIANT(512, 8, 3, 3), PASS_VARIANT(512, 16, 2, 2), PASS_VARIANT(256, 12, 4, 5), PASS_VARIANT(384, 16, 2, 3),
     PASS_VARIANT(256, 16, 3, 4), PASS_VARIANT(384, 8, 4, 4), PASS_VARIANT(256, 16, 3, 5), PASS_VARIANT(512, 16, 2, 3),
+    PASS_VARIANT_C(512, 12, 2, 2, 2), PASS_VARIANT_C(512, 12, 2, 2, 3), PASS_VARIANT_C(512, 12, 2, 2, 6),
+    PASS_VARIANT_C(512, 12, 2, 2, 1), PASS_VARIANT_C(512, 16, 2, 2, 2),
 };
 static const PassVariant &pass_variant(bool pairs) {
   static int idx[2] = {-1, -1};
   if (idx[0] < 0) {
-    idx[0] = idx[1] = 0;
+    // measured best on B200 (2^28 elements per pass): pairs 1.46 ms = 4.40 TB/s, keys only 1.14 ms = 3.75 TB/s
+    const char *defaults[2] = {"512x16b2k2c4", "512x12b2k2c1"};
     const char *names[2] = {getenv("PSC_RADIX_VARIANT_K"), getenv("PSC_RADIX_VARIANT")};
+    for (int m = 0; m < 2; ++m) {
+      idx[m] = 0;
+      for (size_t i = 0; i < sizeof(g_variants) / sizeof(g_variants[0]); ++i)
+        if (!strcmp(defaults[m], g_variants[i].name)) idx[m] = (int)i;
+    }
     for (int m = 0; m < 2; ++m)
       for (size_t i = 0; names[m] && i < sizeof(g_variants) / sizeof(g_variants[0]); ++i)
         if (!strcmp(names[m], g_variants[i].name)) idx[m] = (int)i;
@@ -418,7 +444,7 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
   static int pf_mult = -1, lb_mode = 0;  // prefetch distance in units of resident CTAs (PSC_RADIX_PF, 0 = off)
   if (pf_mult < 0) {
     const char *e = getenv("PSC_RADIX_PF"); pf_mult = e ? atoi(e) : 1;
-    e = getenv("PSC_RADIX_LB"); lb_mode = e ? atoi(e) : 0;
+    e = getenv("PSC_RADIX_LB"); lb_mode = e ? atoi(e) : 64;
   }
   DevBuf<uint64_t> status(ctx, (size_t)tiles * RADIX);
   DevBuf<uint32_t> counter(ctx, 1);

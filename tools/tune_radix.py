@@ -4,8 +4,9 @@ import os, subprocess, sys, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 args = [a for a in sys.argv[1:] if a != "--keys"]
 keys = "--keys" in sys.argv
-VARIANTS = args[1:] or ["512x12b2k2", "512x12b2k3", "384x12b3k3", "384x12b3k4", "512x8b3k3", "512x16b2k2", "256x12b4k5",
-                        "384x16b2k3", "256x16b3k4", "384x8b4k4", "256x16b3k5", "512x16b2k3"]
+VARIANTS = args[1:] or ["512x12b2k2c4", "512x12b2k3c4", "384x12b3k3c4", "384x12b3k4c4", "512x8b3k3c4", "512x16b2k2c4",
+                        "256x12b4k5c4", "384x16b2k3c4", "256x16b3k4c4", "384x8b4k4c4", "256x16b3k5c4", "512x16b2k3c4",
+                        "512x12b2k2c2", "512x12b2k2c3", "512x12b2k2c6", "512x12b2k2c12", "512x16b2k2c8"]
 n = int(args[0]) if args else 1 << 28
 code = ("import sys; sys.path.insert(0, %r); import psascan_b200 as P; c = P.Context(0); "
         "ms = c.bench_radix_pass(%d, 8); print('%%.4f' %% ms)" % (ROOT, n))
