@@ -8,7 +8,7 @@
 // (the gt_end bit) move up by one.  Everything else is new:
 //   round 0   key = the first k renamed symbols packed at b bits each (k*b <= 64), LSD radix
 //             sort of (key, position)
-//   round r   only suffixes still sharing their key stay "active"; key = (group head << 32 |
+//   round r   only suffixes still sharing their key stay "active"; key = (group head << rank bits |
 //             ISA[pos + h] + 1), sorted again, h doubles.
 #include <algorithm>
 #include <cmath>
@@ -245,7 +245,10 @@ __global__ void __launch_bounds__(GP_THREADS)
     if (v == 0 && i0_out) *i0_out = slot;
     if (!act && !touch_all) continue;
     if (MODE != 0) sa[slot] = v;
-    if (isa) isa[v] = hp;
+    // ISA[v] = SA slot of v's group head.  It already holds the head of the previous group (H, in the
+    // key): only members of groups that split off a new head need the random 4-byte write (on
+    // repetitive texts most groups survive the early rounds unsplit)
+    if (isa && (!later || hp != (uint32_t)(kw[k] >> hshift))) isa[v] = hp;
     if (act) {
       keyY[my_off] = (uint64_t)hp;
       valY[my_off] = v;
@@ -253,15 +256,15 @@ __global__ void __launch_bounds__(GP_THREADS)
   }
 }
 
-// next key from the ISA: (group head << 32) | ISA[position + h] + 1, 0 when past the block end
+// next key from the ISA: (group head << rbits) | ISA[position + h] + 1, 0 when past the block end
 __global__ void __launch_bounds__(256)
     second_key_kernel(uint64_t *__restrict__ keyY, const uint32_t *__restrict__ valY, long a,
-                      const uint32_t *__restrict__ isa, long m, long h) {
+                      const uint32_t *__restrict__ isa, long m, long h, int rbits) {
   long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= a) return;
   long p = (long)valY[j] + h;
-  uint32_t r = p < m ? isa[p] + 1u : 0u;
-  keyY[j] = (keyY[j] << 32) | (uint64_t)r;
+  uint32_t r = p < m ? isa[p] + 1u : 0u;  // <= m: fits rbits = bits_for(m)
+  keyY[j] = (keyY[j] << rbits) | (uint64_t)r;
 }
 
 __device__ __forceinline__ uint32_t renamed_code(const uint8_t *__restrict__ text, long m,
@@ -602,11 +605,10 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
         PSC_LAUNCH_CHECK();
         ctx->launches += 2;
       }
-      { KTrace kt(ctx, "second_key"); second_key_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, res->isa.p, m, h); }
+      { KTrace kt(ctx, "second_key"); second_key_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, res->isa.p, m, h, lowb); }
       PSC_LAUNCH_CHECK();
-      for (int b = 0; b < lowb; b += 8) shifts[nsh++] = b;
-      for (int b = 0; b < hpbits; b += 8) shifts[nsh++] = 32 + b;
-      hshift = 32;
+      for (int b = 0; b < lowb + hpbits; b += 8) shifts[nsh++] = b;  // head packed right above the rank: 7 passes up to 2^27
+      hshift = lowb;
       h *= 2;
     }
     ctx->launches++;
