@@ -137,7 +137,6 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
   DevBuf<uint8_t> Mhi[2], Rhi;
   for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, cap); if (hi_plane) Mhi[k].alloc(ctx, cap); }
   if (world > 1) { Rlo.alloc(ctx, cap); if (hi_plane) Rhi.alloc(ctx, cap); }
-  DevBuf<BlockMeta> meta_d(ctx, 1);
   int cur = 0;
   long right_len = 0;
   for (long id = B - 1; id >= 0; --id) {
@@ -146,33 +145,42 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
     const long m = end - beg, t = n - end;
     const int own = owner(id);
     OwnedBlock *ob = mine[id].get();
-    DevBuf<uint32_t> sa_tmp, gtb_tmp;
-    DevBuf<uint8_t> bwt_tmp;
+    // one broadcast per block: [meta | SA | gt_begin bits | BWT] packed into one buffer (every collective
+    // costs a stream synchronisation and a host round trip)
+    DevBuf<uint8_t> pack;
     uint32_t *sa_p, *gtb_p;
     uint8_t *bwt_p = nullptr;
     BlockMeta meta{0, 0, 0};
-    if (own == rank) {
+    if (world == 1) {
       sa_p = ob->sa.p; gtb_p = ob->gtb.p; bwt_p = ob->bwt.p;
       meta = BlockMeta{ob->i0, ob->end_bit, (int)ob->last};
     } else {
-      sa_tmp.alloc(ctx, m); gtb_tmp.alloc(ctx, m / 32 + 2);
-      sa_p = sa_tmp.p; gtb_p = gtb_tmp.p;
-      if (t > 0) { bwt_tmp.alloc(ctx, m); bwt_p = bwt_tmp.p; }
-    }
-    if (world > 1) {
-      h2d(ctx, meta_d.p, &meta, 1);
-      coll(ctx, fn, user, PSC_COLL_BCAST, meta_d.p, sizeof(BlockMeta), own);
-      d2h(ctx, &meta, meta_d.p, 1);
-      coll(ctx, fn, user, PSC_COLL_BCAST, sa_p, (size_t)m * 4, own);
-      coll(ctx, fn, user, PSC_COLL_BCAST, gtb_p, (size_t)(m / 32 + 1) * 4, own);
-      if (t > 0) coll(ctx, fn, user, PSC_COLL_BCAST, bwt_p, (size_t)m, own);
+      const size_t sa_off = 256, gtb_off = sa_off + (((size_t)m * 4 + 255) & ~(size_t)255);
+      const size_t gtb_bytes = (size_t)(m / 32 + 2) * 4;
+      const size_t bwt_off = gtb_off + ((gtb_bytes + 255) & ~(size_t)255);
+      const size_t total = bwt_off + (t > 0 ? (size_t)m : 0);
+      pack.alloc(ctx, total);
+      sa_p = reinterpret_cast<uint32_t *>(pack.p + sa_off);
+      gtb_p = reinterpret_cast<uint32_t *>(pack.p + gtb_off);
+      if (t > 0) bwt_p = pack.p + bwt_off;
+      if (own == rank) {
+        meta = BlockMeta{ob->i0, ob->end_bit, (int)ob->last};
+        h2d(ctx, reinterpret_cast<BlockMeta *>(pack.p), &meta, 1);
+        PSC_CUDA(cudaMemcpyAsync(sa_p, ob->sa.p, (size_t)m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        PSC_CUDA(cudaMemcpyAsync(gtb_p, ob->gtb.p, gtb_bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+        if (t > 0) PSC_CUDA(cudaMemcpyAsync(bwt_p, ob->bwt.p, (size_t)m, cudaMemcpyDeviceToDevice, ctx->stream));
+        sync(ctx);          // `meta` is a stack variable
+        mine[id].reset();   // the packed copy is what the rest of the level uses
+      }
+      coll(ctx, fn, user, PSC_COLL_BCAST, pack.p, total, own);
+      d2h(ctx, &meta, reinterpret_cast<BlockMeta *>(pack.p), 1);
       sync(ctx);
     }
     const long i0 = (long)meta.i0;
     PSC_CUDA(cudaMemsetAsync(gt_new, 0, gwords * 4, ctx->stream));
     DevBuf<uint32_t> gap;
     if (t > 0) {
-      gap.alloc(ctx, m + 1);
+      gap.alloc(ctx, m + 1 + (world > 1 ? (n >> 5) + 2 - ((end - 1) >> 5) : 0));
       gap.zero();
       psc_rank *rk = rank_build(ctx, bwt_p, m, i0);
       try {
@@ -187,11 +195,12 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
       } catch (...) { rank_free(rk); throw; }
       rank_free(rk);
       if (world > 1) {
-        coll(ctx, fn, user, PSC_COLL_ALLREDUCE_SUM_U32, gap.p, (size_t)(m + 1) * 4, 0);
-        if (id > 0) {  // disjoint bits of disjoint tail ranges: SUM == OR
-          long w0 = (end - 1) >> 5, w1 = (n >> 5) + 1;
-          coll(ctx, fn, user, PSC_COLL_ALLREDUCE_SUM_U32, gt_new + w0, (size_t)(w1 - w0) * 4, 0);
-        }
+        // gap counts and (disjoint bits of disjoint tail ranges: SUM == OR) the new gt bits in ONE all-reduce:
+        // the gt words ride behind the gap array
+        const long w0 = (end - 1) >> 5, w1 = (n >> 5) + 1, gw = id > 0 ? w1 - w0 : 0;
+        if (gw) PSC_CUDA(cudaMemcpyAsync(gap.p + m + 1, gt_new + w0, (size_t)gw * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        coll(ctx, fn, user, PSC_COLL_ALLREDUCE_SUM_U32, gap.p, (size_t)(m + 1 + gw) * 4, 0);
+        if (gw) PSC_CUDA(cudaMemcpyAsync(gt_new + w0, gap.p + m + 1, (size_t)gw * 4, cudaMemcpyDeviceToDevice, ctx->stream));
       }
     }
     if (id > 0) {
