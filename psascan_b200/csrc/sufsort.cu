@@ -29,12 +29,24 @@ __global__ void __launch_bounds__(256)
   __shared__ uint32_t sh[257];
   for (int i = threadIdx.x; i < 257; i += blockDim.x) sh[i] = 0;
   __syncthreads();
-  long stride = (long)gridDim.x * blockDim.x;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += stride) {
-    int c = text[i];
+  auto count = [&](int c, long i) {
     atomicAdd(&sh[c], 1u);
     if (c == last && i < m - 1 && gt_end != nullptr && !bit_get(gt_end, i + 1)) atomicAdd(&sh[256], 1u);
+  };
+  // 16 symbols per load where the address allows it, single bytes at both ends
+  const long head = min(m, (long)((16 - ((uintptr_t)text & 15)) & 15));
+  const long nvec = (m - head) / 16;
+  const long gtid = (long)blockIdx.x * blockDim.x + threadIdx.x, stride = (long)gridDim.x * blockDim.x;
+  const uint4 *v = reinterpret_cast<const uint4 *>(text + head);
+  for (long q = gtid; q < nvec; q += stride) {
+    const uint4 x = __ldg(v + q);
+    const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+    const long i0 = head + q * 16;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) count((int)((w[j >> 2] >> (8 * (j & 3))) & 255), i0 + j);
   }
+  for (long i = gtid; i < head; i += stride) count(text[i], i);
+  for (long i = head + nvec * 16 + gtid; i < m; i += stride) count(text[i], i);
   __syncthreads();
   for (int i = threadIdx.x; i < 257; i += blockDim.x)
     if (sh[i]) atomicAdd(&hist[i], (unsigned long long)sh[i]);
