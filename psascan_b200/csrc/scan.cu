@@ -39,8 +39,7 @@ __global__ void __launch_bounds__(SC_THREADS)
 }
 
 // Tile aggregates -> exclusive prefixes, in place, by ONE block: 1024 threads x 8 consecutive
-// aggregates per step (a sum array and/or a running-max array; the prefix-doubling grouping needs
-// both at once).  The tile kernels before and after it carry the real traffic.
+// aggregates per step.  The tile kernels before and after it carry the real traffic.
 constexpr int AG_THREADS = 1024;
 constexpr int AG_ITEMS = 8;
 
@@ -94,22 +93,11 @@ __global__ void __launch_bounds__(AG_THREADS)
   if (SUM && threadIdx.x == 0 && total_out) *total_out = carry_s;
 }
 
-void scan_aggregates_sum_max(psc_context *ctx, uint64_t *asum_d, uint64_t *amax_d, long n, uint64_t *total_d) {
-  scan_aggregates_kernel<true, true><<<1, AG_THREADS, 0, ctx->stream>>>(asum_d, amax_d, n, total_d);
-  PSC_LAUNCH_CHECK();
-  ctx->launches++;
-}
 void scan_aggregates_sum(psc_context *ctx, uint64_t *agg_d, long n, uint64_t *total_d) {
   scan_aggregates_kernel<true, false><<<1, AG_THREADS, 0, ctx->stream>>>(agg_d, nullptr, n, total_d);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
 }
-void scan_aggregates_max(psc_context *ctx, uint64_t *agg_d, long n) {
-  scan_aggregates_kernel<false, true><<<1, AG_THREADS, 0, ctx->stream>>>(nullptr, agg_d, n, nullptr);
-  PSC_LAUNCH_CHECK();
-  ctx->launches++;
-}
-
 void exclusive_scan_u32_to_u64(psc_context *ctx, const uint32_t *in, uint64_t *out, long n,
                                uint64_t *total_d) {
   if (n <= 0) {
