@@ -556,7 +556,8 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
   int out = 0;  // which (kbuf, vbuf) pair the next compaction writes
   long a = m, h = k;
   const int hpbits = bits_for((uint64_t)(m > 1 ? m - 1 : 1)), lowb = bits_for((uint64_t)m);
-  bool text_round_done = false;
+  int text_rounds = 0, max_text_rounds = 6;
+  if (const char *e = getenv("PSC_TEXT_ROUNDS")) max_text_rounds = atoi(e);
   DevBuf<unsigned long long> gp_total(ctx, 1);
   int hshift = -1;  // round 0: SA slot = index
   for (int round = 0;; ++round) {
@@ -584,9 +585,11 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
     uint32_t *VY = vbuf[out];
     int nsh = 0;
     const int k1 = (64 - hpbits) / lut.bits;
-    if (!text_round_done && k1 >= 1) {
-      // text round: extend the compared prefix by k1 symbols read from the text (no ISA yet)
-      text_round_done = true;
+    // text round: extend the compared prefix by k1 symbols read from the text (no ISA yet).  Always the first
+    // choice after round 0; repeated while only a few suffixes (< m/32) are still tied, because a text round
+    // costs O(a) and the first doubling round costs the m-element ISA (1.4 ms per 2^27 on top of its own sort)
+    if (k1 >= 1 && res->isa.p == nullptr && text_rounds < max_text_rounds && (text_rounds == 0 || a * 32 <= m)) {
+      ++text_rounds;
       { KTrace kt(ctx, "second_key_text"); second_key_text_kernel<<<(unsigned)div_up(a, 256), 256, 0, ctx->stream>>>(KY, VY, a, text_d, m, gt_end_bits_d,
                                                                                 lut, h, k1); }
       PSC_LAUNCH_CHECK();
@@ -594,7 +597,6 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
       hshift = k1 * lut.bits;
       h += k1;
     } else {
-      text_round_done = true;
       if (res->isa.p == nullptr) {
         // first doubling round: now the full inverse suffix array is needed
         res->isa.alloc(ctx, m);
