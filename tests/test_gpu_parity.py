@@ -71,6 +71,18 @@ def test_sort_modes_8bit_codes(ctx, monkeypatch, env, sigma):
     assert np.array_equal(decode_sa5(ctx.construct_sa(text, max_block=30000)), want)
 
 
+@pytest.mark.parametrize("rounds", ["0", "1", "6"])
+def test_text_round_policy(ctx, monkeypatch, rounds):
+    """After round 0 the sorter extends tied suffixes by symbols read from the text, again and again while
+    few are tied, before it pays for the ISA and doubles: no text round, one, or up to six must all give the SA."""
+    monkeypatch.setenv("PSC_TEXT_ROUNDS", rounds)
+    for text in (textgen.markov(60000, seed=11), textgen.repetitive(50000, seed=4, seed_len=2000, rate=2e-3),
+                 textgen.dna(40000, seed=12)):
+        want = O.sa(text)
+        assert np.array_equal(decode_sa5(ctx.construct_sa(text)), want)
+        assert np.array_equal(decode_sa5(ctx.construct_sa(text, max_block=17000)), want)
+
+
 def test_sentinel_255_rejected(ctx):
     import psascan_b200 as P
     text = textgen.dna(5000).copy()
