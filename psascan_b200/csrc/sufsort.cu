@@ -56,8 +56,10 @@ struct RenameLut {
   uint16_t code[256];  // dense code (1..sigma') of the renamed symbol; for c == last: the LOW code
   uint16_t code_last_high;
   int last;
-  int bits;  // bits per code
-  int k;     // symbols per key
+  int bits;  // bits per code (1-based codes, 0 = past the block end)
+  int k;     // symbols per round-0 key
+  int kbits; // bits per symbol in the round-0 key: `bits`, or one less in dense mode
+  int dense; // 1: the round-0 key packs code - 1 (sigma is a power of two, see sort_block)
 };
 
 // ---- round 0 keys --------------------------------------------------------------------------
@@ -87,11 +89,12 @@ __global__ void __launch_bounds__(SC_THREADS)
       cd = scode[c];
       if (c == lut.last && (i == m - 1 || gt_end == nullptr || bit_get(gt_end, i + 1)))
         cd = lut.code_last_high;
+      cd -= (uint16_t)lut.dense;
     }
     codes[code_slot(e)] = cd;
   }
   __syncthreads();
-  const int k = lut.k, bits = lut.bits;
+  const int k = lut.k, bits = lut.kbits;
   const uint64_t mask = (k * bits >= 64) ? ~0ull : ((1ull << (k * bits)) - 1ull);
   // two consecutive positions per thread and step (rolling update for the second one): one 16-byte
   // store per lane, a warp writes 512 contiguous bytes
@@ -300,10 +303,17 @@ __global__ void __launch_bounds__(256)
   __syncthreads();
   long j = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= a) return;
-  long p = (long)valY[j] + h;
+  const long v = (long)valY[j], p = v + h;
   uint64_t key = keyY[j];
-  for (int s = 0; s < k1; ++s)
-    key = (key << lut.bits) | renamed_code(text, m, gt_end, scode, lut.last, lut.code_last_high, p + s);
+  if (p >= m) {
+    // a suffix that ended inside the prefix compared so far: in dense mode its padding looked like the
+    // smallest symbol, so several of them (and longer suffixes) can share a group.  It sorts before every
+    // suffix that goes on (their first code below is >= 1), the shorter one first.
+    key = (key << (k1 * lut.bits)) | (uint64_t)(m - 1 - v);
+  } else {
+    for (int s = 0; s < k1; ++s)
+      key = (key << lut.bits) | renamed_code(text, m, gt_end, scode, lut.last, lut.code_last_high, p + s);
+  }
   keyY[j] = key;
 }
 
@@ -444,7 +454,17 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
     }
   }
   lut.bits = bits_for((uint64_t)sigma);
-  int kmax = 64 / lut.bits;
+  int max_text_rounds = 6;
+  if (const char *e = getenv("PSC_TEXT_ROUNDS")) max_text_rounds = atoi(e);
+  // dense mode: when the renamed alphabet has exactly 2^b symbols the round-0 key packs code - 1 at b bits
+  // instead of code at b + 1 (200 MB of DNA in one block: 16 symbols in 32 bits, 4 digit passes instead of 6).
+  // The padding of suffixes shorter than k then equals the smallest symbol: such a suffix may share a group
+  // with longer ones, and the text round (always the next round) puts it first (second_key_text_kernel).
+  const int k1_text = (64 - bits_for((uint64_t)(m > 1 ? m - 1 : 1))) / lut.bits;  // symbols a text round adds
+  lut.dense = (sigma >= 2 && (sigma & (sigma - 1)) == 0 && lut.bits <= 7 && max_text_rounds >= 1 &&
+               k1_text >= 2 && (k1_text - 1) * lut.bits >= 7 && !getenv("PSC_NO_DENSE")) ? 1 : 0;
+  lut.kbits = lut.bits - lut.dense;
+  int kmax = 64 / lut.kbits;
   // smallest k with m * p2^k <= 1/16 (expected share of suffixes still tied after round 0)
   int k = 1;
   {
@@ -452,10 +472,10 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
     while (k < kmax && v * p2 > 1.0) { v *= p2; ++k; }
     if (v * p2 > 1.0) k = kmax;
   }
-  int passes = (k * lut.bits + 7) / 8;
-  k = std::min(kmax, (passes * 8) / lut.bits);  // fill the last digit
+  int passes = (k * lut.kbits + 7) / 8;
+  k = std::min(kmax, (passes * 8) / lut.kbits);  // fill the last digit
   if (k > m) k = (int)std::max<long>(1, m);
-  passes = (k * lut.bits + 7) / 8;
+  passes = (k * lut.kbits + 7) / 8;
   lut.k = k;
 
   DevBuf<uint64_t> keyA(ctx, m), keyB(ctx, m);
@@ -556,8 +576,7 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
   int out = 0;  // which (kbuf, vbuf) pair the next compaction writes
   long a = m, h = k;
   const int hpbits = bits_for((uint64_t)(m > 1 ? m - 1 : 1)), lowb = bits_for((uint64_t)m);
-  int text_rounds = 0, max_text_rounds = 6;
-  if (const char *e = getenv("PSC_TEXT_ROUNDS")) max_text_rounds = atoi(e);
+  int text_rounds = 0;
   DevBuf<unsigned long long> gp_total(ctx, 1);
   int hshift = -1;  // round 0: SA slot = index
   for (int round = 0;; ++round) {

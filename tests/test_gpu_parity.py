@@ -83,6 +83,24 @@ def test_text_round_policy(ctx, monkeypatch, rounds):
         assert np.array_equal(decode_sa5(ctx.construct_sa(text, max_block=17000)), want)
 
 
+@pytest.mark.parametrize("sigma", [2, 4, 16, 64])
+def test_dense_round0_codes(ctx, sigma):
+    """Alphabets of exactly 2^b symbols (one block, no renaming split): round 0 packs code - 1 at b bits, so the
+    padding of the last few suffixes equals the smallest symbol; texts that END in runs of the smallest symbol
+    (and contain longer runs of it elsewhere) are where that matters."""
+    rng = np.random.default_rng(100 + sigma)
+    for n, tail in ((50001, 0), (40000, 1), (40000, 7), (40000, 70), (3000, 200)):
+        text = rng.integers(0, sigma, size=n, dtype=np.uint8)
+        text[1000:1300] = 0
+        text[20000 % n:20000 % n + 90] = 0
+        if tail:
+            text[-tail:] = 0
+        assert len(np.unique(text)) == sigma
+        assert np.array_equal(decode_sa5(ctx.construct_sa(text)), O.sa(text)), (sigma, n, tail)
+        text2 = (sigma - 1 - text).astype(np.uint8)          # ends in the LARGEST symbol instead
+        assert np.array_equal(decode_sa5(ctx.construct_sa(text2)), O.sa(text2)), (sigma, n, tail, "mirrored")
+
+
 def test_sentinel_255_rejected(ctx):
     import psascan_b200 as P
     text = textgen.dna(5000).copy()
