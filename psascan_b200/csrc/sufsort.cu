@@ -463,6 +463,10 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
   const int k1_text = (64 - bits_for((uint64_t)(m > 1 ? m - 1 : 1))) / lut.bits;  // symbols a text round adds
   lut.dense = (sigma >= 2 && (sigma & (sigma - 1)) == 0 && lut.bits <= 7 && max_text_rounds >= 1 &&
                k1_text >= 2 && (k1_text - 1) * lut.bits >= 7 && !getenv("PSC_NO_DENSE")) ? 1 : 0;
+  // the same for exactly 256 renamed symbols (255 byte values plus the split of the block's last symbol, i.e.
+  // every block with a tail of a text that uses all byte values): 8-bit codes keep the key-building pass
+  const bool dense8 = (sigma == 256 && m >= 64 && max_text_rounds >= 1 && k1_text >= 2 && !getenv("PSC_NO_DENSE"));
+  if (dense8) lut.dense = 1;
   lut.kbits = lut.bits - lut.dense;
   int kmax = 64 / lut.kbits;
   // smallest k with m * p2^k <= 1/16 (expected share of suffixes still tied after round 0)
@@ -491,7 +495,8 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
   // histogram shifted by a few positions (computed here instead of `passes` shared atomics per suffix
   // in a kernel), and the first digit pass builds its keys straight from the text (radix.cu, KEYGEN):
   // no key array is written and read back before the sort.
-  const bool codes8 = (lut.bits == 8 && m >= 64);
+  const bool codes8 = (lut.kbits == 8 && m >= 64);
+  const int dn = codes8 ? lut.dense : 0;  // round-0 code = code - dn
   if (codes8) {
     uint8_t head[8];
     uint32_t gw = 0xffffffffu;
@@ -501,15 +506,16 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
     unsigned long long ch[256] = {0};
     for (int c = 0; c < 256; ++c) {
       if (c == last) {
-        if (hist[256]) ch[lut.code[c]] += hist[256];
-        ch[lut.code_last_high] += hist[c] - hist[256];
-      } else if (hist[c]) ch[lut.code[c]] += hist[c];
+        if (hist[256]) ch[lut.code[c] - dn] += hist[256];
+        ch[lut.code_last_high - dn] += hist[c] - hist[256];
+      } else if (hist[c]) ch[lut.code[c] - dn] += hist[c];
     }
     int hc[8];
     for (int j = 0; j < 8; ++j) {
       int c = head[j];
       hc[j] = lut.code[c];
       if (c == last && (gt_end_bits_d == nullptr || ((gw >> (j + 1)) & 1u))) hc[j] = lut.code_last_high;
+      hc[j] -= dn;
     }
     // packed mode: the position rides in the low bits of the key (8 B per element and pass instead of
     // 12) when all k symbols still fit above it.  (With fewer key bits -- the last symbol kept only in
@@ -538,9 +544,9 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
     KeyGen kg;
     memset(&kg, 0, sizeof(kg));
     kg.text = text_d; kg.gt_end = gt_end_bits_d; kg.m = m;
-    kg.last = last; kg.code_last_high = lut.code_last_high;
+    kg.last = last; kg.code_last_high = lut.code_last_high - dn;
     kg.dshift = 64 - 8 * S; kg.kshift = 64 - kbits; kg.vbits = packed ? pbits : 0;
-    for (int c = 0; c < 256; ++c) kg.code[c] = (uint8_t)lut.code[c];
+    for (int c = 0; c < 256; ++c) kg.code[c] = (uint8_t)(lut.code[c] - dn);
     uint64_t key0 = 0;
     for (int j = 0; j < 8; ++j) key0 = (key0 << 8) | (uint64_t)hc[j];
     key0 >>= kg.kshift;
