@@ -102,6 +102,73 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// Alphabets of more than 32 symbols: one block per chunk of 32 sectors (7168 symbols) writes ALL planes.  The
+// lanes holding the same symbol are found ONCE per 32 symbols and kept in registers; the planes are then
+// written 32 symbols (codes) at a time through 28 KB of shared memory.  (rank_fill_kernel above, one block per
+// chunk AND group of 32 codes, repeats loads and ballots for each group: 3 x 512 MiB of random bytes 217 -> 156 ms;
+// for up to 32 symbols the simpler kernel is the faster one, 6.5 against 8.4 ms on 8 x 128 MiB of Markov text.)
+__global__ void __launch_bounds__(256)
+    rank_fill_all_kernel(const uint8_t *__restrict__ bwt, long m, long i0, CodeLut lut, int n_codes, int code_bits,
+                         long n_sectors, const uint32_t *__restrict__ cc, const uint8_t *sym_of_code,
+                         uint32_t *__restrict__ sectors) {
+  __shared__ uint8_t codes[RK_CHUNK];
+  __shared__ uint32_t words[RK_GROUP][RK_CHUNK_SECTORS][7];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long chunk = blockIdx.x;
+  const long beg = chunk * RK_CHUNK;
+  for (int e = tid; e < RK_CHUNK; e += 256) {
+    long i = beg + e;
+    codes[e] = (i < m && i != i0) ? lut.code[bwt[i]] : (uint8_t)0xFF;
+  }
+  __syncthreads();
+  constexpr int PER_WARP = (RK_CHUNK_SECTORS / 8) * 7;  // (sector, word) pairs of a warp
+  uint32_t mk[PER_WARP];                                // lanes with my symbol, kept by the lowest of them only
+  uint8_t cd[PER_WARP];
+#pragma unroll
+  for (int q = 0; q < PER_WARP; ++q) {
+    const int s = warp + (q / 7) * 8, g = q % 7;
+    const int code = codes[s * RK_BITS + g * 32 + lane];
+    uint32_t mask = __ballot_sync(0xffffffffu, code != 0xFF);
+    if (code == 0xFF) mask = ~mask;
+    for (int b = 0; b < code_bits; ++b) {
+      const bool bit = (code >> b) & 1;
+      const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+      mask &= bit ? bal : ~bal;
+    }
+    cd[q] = (uint8_t)code;
+    mk[q] = (code != 0xFF && lane == __ffs(mask) - 1) ? mask : 0u;
+  }
+  for (int gbase = 0; gbase < n_codes; gbase += RK_GROUP) {
+    for (int e = tid; e < RK_GROUP * RK_CHUNK_SECTORS * 7; e += 256) (&words[0][0][0])[e] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < PER_WARP; ++q) {
+      const int cl = (int)cd[q] - gbase;
+      if (mk[q] && cl >= 0 && cl < RK_GROUP) words[cl][warp + (q / 7) * 8][q % 7] = mk[q];
+    }
+    __syncthreads();
+    for (int cl = warp; cl < RK_GROUP; cl += 8) {
+      int code = gbase + cl;
+      if (code >= n_codes) break;
+      uint32_t w[7];
+      uint32_t pc = 0;
+#pragma unroll
+      for (int g = 0; g < 7; ++g) { w[g] = words[cl][lane][g]; pc += __popc(w[g]); }
+      uint32_t incl = pc;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+      uint32_t before = cc[(size_t)chunk * 256 + sym_of_code[code]] + incl - pc;
+      long s = chunk * RK_CHUNK_SECTORS + lane;
+      if (s < n_sectors) {
+        uint4 *out = reinterpret_cast<uint4 *>(sectors + ((size_t)code * (size_t)n_sectors + s) * 8);
+        out[0] = make_uint4(before, w[0], w[1], w[2]);
+        out[1] = make_uint4(w[3], w[4], w[5], w[6]);
+      }
+    }
+    __syncthreads();
+  }
+}
+
 psc_rank *rank_build(psc_context *ctx, const uint8_t *bwt_d, long m, long i0) {
   PhaseTimer timer(ctx, &ctx->stats.ms_rank_build);
   psc_rank *r = new psc_rank();
@@ -143,11 +210,14 @@ psc_rank *rank_build(psc_context *ctx, const uint8_t *bwt_d, long m, long i0) {
   if (nc > 0) {
     DevBuf<uint8_t> soc(ctx, 256);
     h2d(ctx, soc.p, sym_of_code, 256);
-    dim3 grid((unsigned)nchunks, (unsigned)div_up(nc, RK_GROUP));
     int code_bits = 1;
     while ((1 << code_bits) < nc) ++code_bits;
-    rank_fill_kernel<<<grid, 256, 0, ctx->stream>>>(bwt_d, m, i0, lut, nc, code_bits, r->n_sectors, cc.p, soc.p,
-                                                    r->sectors_d);
+    if (nc <= RK_GROUP)
+      rank_fill_kernel<<<dim3((unsigned)nchunks, 1), 256, 0, ctx->stream>>>(bwt_d, m, i0, lut, nc, code_bits, r->n_sectors,
+                                                                             cc.p, soc.p, r->sectors_d);
+    else
+      rank_fill_all_kernel<<<(unsigned)nchunks, 256, 0, ctx->stream>>>(bwt_d, m, i0, lut, nc, code_bits, r->n_sectors,
+                                                                        cc.p, soc.p, r->sectors_d);
     PSC_LAUNCH_CHECK();
     sync(ctx);  // sym_of_code is a stack array
   }
