@@ -145,11 +145,12 @@ def _worker(rank, world, port, q):
         dist.destroy_process_group()
 
 
-def test_two_rank_schedule_and_collectives():
-    world = 2
+@pytest.mark.parametrize("world", [2, 3])
+def test_schedule_and_collectives(world):
+    """world 2, and 3 for shares that do not divide evenly (ragged all-to-all splits, empty overlaps)"""
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29500 + (os.getpid() % 2000)
+    port = 29500 + (os.getpid() % 2000) + world
     procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
