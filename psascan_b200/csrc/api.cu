@@ -217,7 +217,7 @@ static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, lon
   if (B > 1) {
     Ga.alloc(ctx, gwords); Gb.alloc(ctx, gwords);
     Ga.zero(); Gb.zero();
-    for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); if (n > (1L << 32)) Mhi[k].alloc(ctx, n);  /* high bytes only above 4 GiB */ }
+    for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); if (need_hi_plane(n)) Mhi[k].alloc(ctx, n);  /* high bytes only above 4 GiB */ }
   }
   uint32_t *gt_cur = Ga.p, *gt_new = Gb.p;
   int cur = 0;

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <string>
 #include <chrono>
@@ -28,6 +29,9 @@ struct CudaError { int code; };
 #define PSC_LAUNCH_CHECK() PSC_CUDA(cudaGetLastError())
 
 static inline long div_up(long a, long b) { return (a + b - 1) / b; }
+// the merged SA keeps a high-byte plane only for texts above 4 GiB; PSC_FORCE_HI=1 turns it on for small
+// texts (tests: the 40-bit paths of merge and writer)
+static inline bool need_hi_plane(long n) { return n > (1L << 32) || getenv("PSC_FORCE_HI") != nullptr; }
 
 }  // namespace psc
 

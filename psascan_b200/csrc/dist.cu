@@ -131,7 +131,7 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
   Ga.zero(); Gb.zero();
   uint32_t *gt_cur = Ga.p, *gt_new = Gb.p;
   // my share of the merged sequence (double buffered) and what arrives from the other ranks per level
-  const bool hi_plane = n > (1L << 32);  // high bytes only above 4 GiB
+  const bool hi_plane = need_hi_plane(n);  // high bytes only above 4 GiB
   const long cap = share_begin(1, n, world) + 16;
   DevBuf<uint32_t> Mlo[2], Rlo;
   DevBuf<uint8_t> Mhi[2], Rhi;
@@ -361,7 +361,7 @@ void construct_sa_pipelined(psc_context *ctx, const uint8_t *text_d, long n, lon
   uint32_t *gt_cur = Ga.p, *gt_new = Gb.p;
   DevBuf<uint32_t> Mlo[2];
   DevBuf<uint8_t> Mhi[2];
-  for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); if (n > (1L << 32)) Mhi[k].alloc(ctx, n);  /* high bytes only above 4 GiB */ }
+  for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); if (need_hi_plane(n)) Mhi[k].alloc(ctx, n);  /* high bytes only above 4 GiB */ }
   int cur = 0;
   long right_len = 0;
   for (long id = B - 1; id >= 0; --id) {
