@@ -101,6 +101,21 @@ def test_dense_round0_codes(ctx, sigma):
         assert np.array_equal(decode_sa5(ctx.construct_sa(text2)), O.sa(text2)), (sigma, n, tail, "mirrored")
 
 
+def test_high_byte_plane_forced(ctx, monkeypatch):
+    """Texts above 4 GiB keep a ninth..fortieth bit plane through the merge and the 40-bit writer; PSC_FORCE_HI
+    switches that path on for small texts (all high bytes are 0, the code path is the one of big texts)."""
+    import torch
+    monkeypatch.setenv("PSC_FORCE_HI", "1")
+    for name, gen, kw, n, sa5 in CASES[:4]:
+        text = golden_text(gen, kw, n)
+        assert np.array_equal(ctx.construct_sa(text, max_block=n // 3 + 5), sa5), name
+        d_text = torch.from_numpy(text).cuda()
+        d_out = torch.zeros(5 * n, dtype=torch.uint8, device="cuda")
+        ctx.construct_sa_dist_ptr(d_text.data_ptr(), n, d_out.data_ptr(), 1000)
+        torch.cuda.synchronize()
+        assert np.array_equal(d_out.cpu().numpy(), sa5), (name, "dist schedule")
+
+
 def test_sentinel_255_rejected(ctx):
     import psascan_b200 as P
     text = textgen.dna(5000).copy()
