@@ -245,7 +245,12 @@ void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, con
     int bshift = 22;  // 4 Mi counters = 16 MB of gap array per bucket
     while (((r->m + 1) >> bshift) + 1 > WK_MAX_BUCKETS) ++bshift;
     const int nb = (int)(((r->m + 1) >> bshift) + 1);
-    DevBuf<uint32_t> emit(ctx, T), part(ctx, T);
+    // scratch sized to the next power of two (at least 2^24): the last chunk of every tail has its own length,
+    // and a fresh pair of up to 2 GB buffers per length cost more than the walk on multi-GiB texts (6 GiB of
+    // DNA, 11 blocks: 111 GB of cached buffers, trimmed and reallocated under memory pressure)
+    long scratch = 1L << 24;
+    while (scratch < T) scratch <<= 1;
+    DevBuf<uint32_t> emit(ctx, scratch), part(ctx, scratch);
     DevBuf<unsigned long long> bc(ctx, WK_MAX_BUCKETS), cur(ctx, WK_MAX_BUCKETS);
     bc.zero();
     { KTrace kt(ctx, "lf_walk(emit)"); lf_walk_kernel<2><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d, start_rank_d,
