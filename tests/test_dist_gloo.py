@@ -170,3 +170,61 @@ def test_plan_helpers():
             assert shares[0][0] == 0 and shares[-1][1] == t
             for a, b in zip(shares, shares[1:]):
                 assert a[1] == b[0] and a[1] % 32 == 0 or a[1] == t
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 5, 8])
+def test_sharded_merge_plan_simulated(world):
+    """The exchange plan of the sharded merge (csrc/dist.cu: share boundaries, block suffixes before each
+    boundary, who sends which part of its share to whom) simulated for all ranks in one process, on random
+    gap arrays including empty shares (fewer slots than ranks) and lopsided interleavings."""
+    from psascan_b200 import dist as D
+    rng = np.random.default_rng(world)
+    ov = lambda a0, a1, b0, b1: max(0, min(a1, b1) - max(a0, b0))
+    for trial in range(30):
+        nblocks = int(rng.integers(2, 6))
+        sizes = [int(rng.integers(1, 40)) for _ in range(nblocks)]
+        # a random "suffix array": global order of all positions; block b owns positions [beg_b, beg_b + m_b)
+        n = sum(sizes)
+        order = rng.permutation(n) if trial % 3 else np.arange(n)          # also the all-left-first extreme
+        begs = np.concatenate([[0], np.cumsum(sizes)])[:-1]
+        rank_of = np.empty(n, dtype=np.int64); rank_of[order] = np.arange(n)
+        shards = [np.zeros(0, dtype=np.int64) for _ in range(world)]
+        R = 0
+        for b in range(nblocks - 1, -1, -1):
+            m, beg = sizes[b], int(begs[b])
+            mine = np.arange(beg, beg + m)
+            psa = mine[np.argsort(rank_of[mine])] - beg                    # block-relative SA
+            right = np.arange(beg + m, n)
+            # gap[u] = number of right-side suffixes between block suffixes u-1 and u
+            rr = np.sort(rank_of[right]); br = rank_of[psa + beg]
+            gap = np.diff(np.concatenate([[0], np.searchsorted(rr, br), [len(rr)]]))
+            L = R + m
+            Q = [D.share_begin(g, L, world) for g in range(world + 1)]
+            if R == 0:
+                shards = [beg + psa[Q[g]:Q[g + 1]] for g in range(world)]
+            else:
+                E = np.concatenate([[0], np.cumsum(gap)])[:m + 1]
+                A = np.arange(m + 1) + E
+                cnt = [int(np.searchsorted(A, q, side="right")) - 1 for q in Q]
+                ra = [q - c for q, c in zip(Q, cnt)]
+                P = [D.share_begin(g, R, world) for g in range(world + 1)]
+                assert ra[0] == 0 and ra[world] == R and all(x <= y for x, y in zip(ra, ra[1:]))
+                new = []
+                slot = np.arange(m) + E[1:m + 1]
+                for g in range(world):
+                    recv = np.concatenate([shards[h][max(P[h], ra[g]) - P[h]:max(P[h], ra[g]) - P[h] + ov(P[h], P[h + 1], ra[g], ra[g + 1])]
+                                           for h in range(world)]) if world else np.zeros(0, dtype=np.int64)
+                    a, bnd = Q[g], Q[g + 1]
+                    out = np.empty(bnd - a, dtype=np.int64)
+                    is_blk = np.zeros(bnd - a, dtype=bool)
+                    sel = (slot >= a) & (slot < bnd)
+                    is_blk[slot[sel] - a] = True
+                    out[is_blk] = beg + psa[sel]
+                    assert (~is_blk).sum() == len(recv) == ra[g + 1] - ra[g]
+                    out[~is_blk] = recv
+                    new.append(out)
+                shards = new
+            R = L
+            assert [len(x) for x in shards] == [Q[g + 1] - Q[g] for g in range(world)]
+        merged = np.concatenate(shards)
+        assert np.array_equal(merged, np.argsort(rank_of)), (world, trial)
