@@ -1,21 +1,29 @@
 #!/usr/bin/env python
-"""bench.py -- SA construction throughput of the B200 hot path (BASELINE.json metric).
+"""bench.py -- SA construction throughput and LF steps/s of the B200 hot path (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--size BYTES]
-                  [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--size BYTES] [--impl reference]
 
 A step = one SA construction over one synthetic text (text -> 40-bit .sa5 entries).
-  value : input MB/s with the text and the output resident in HBM (device time, CUDA events
-          recorded by the library on its own stream around the whole construction)
-  e2e   : the same through the host-buffer C-ABI call psc_construct_sa (pinned host text in,
-          .sa5 bytes out to pinned host memory; both copies inside the timed region)
-N > 1: one process per GPU (torchrun), each rank builds the SA of its own text of the same shape
-(the single-block configuration does not shard: "replicas", weak scaling).
---impl reference times the unmodified reference construct_sa (oracle/_ref) on the host cores.
+Default workload: the configs[2] generator (order-5 Markov, 30 symbols) at 2 GiB in 8 blocks of 256 MiB,
+the largest multiple-of-8-blocks size whose text, block suffix arrays, gap arrays and output stay resident
+in one B200 with room for the e2e leg's pinned buffers; it runs the whole pSAscan
+pipeline (block sorts, rank structures, 7.5 G LF steps, gap-guided merge).
+  value : input MB/s with the text and the output resident in HBM (device time, CUDA events recorded
+          by the library on its own stream around the whole construction)
+  e2e   : the same through the host-buffer entry point (pinned host text in, .sa5 bytes out to pinned
+          host memory; both copies inside the timed region)
+N > 1: one process per GPU (torchrun), the SAME text sharded over the ranks (csrc/dist.cu: block sorts on
+separate GPUs, the tail walk of every block split over the ranks, gap counts summed over NVLink, merge
+sharded by output range): strong scaling.  Every rank keeps n/N of the suffix array.
+After the timed loops the last result is verified on the device (psc_verify_sa_d, O(n)); a wrong
+suffix array makes the run fail.
+--impl reference times the unmodified reference construct_sa (oracle/_ref) on the host cores, on the
+same full text.
 """
 import argparse
 import json
 import os
+import re
 import subprocess
 import sys
 import tempfile
@@ -28,6 +36,9 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 WORKLOADS = {
     # name: (generator, kwargs, default size, max_block (0 = whole text), description)
+    "markov8": ("markov", dict(seed=3), 1 << 31, 1 << 28,
+                "configs[2] generator (order-5 Markov, 30 symbols, seed 3) at 2 GiB in 8 blocks of 256 MiB: "
+                "block sorts + rank structures + 7.5 G LF steps + gap-guided merge"),
     "random1g": ("random", dict(seed=2), 1 << 30, 0,
                  "configs[1]: 1 GiB uniform-random bytes (sigma=255), single block in HBM"),
     "dna200m": ("dna", dict(seed=1), 200_000_000, 0, "configs[0]: 200 MB DNA-like (sigma=4), single block"),
@@ -36,25 +47,37 @@ WORKLOADS = {
     "repetitive_multi": ("repetitive", dict(seed=4), 1 << 28, 1 << 26,
                          "configs[3] scaled: mutated copies of a 1 MiB seed, 4 blocks"),
 }
+DEFAULT_WORKLOAD = "markov8"
+METRIC = "SA construction input MB/s"
 
 
-def gen_text(workload, size, rank):
+def gen_text(workload, size):
+    """the workload's text as a numpy array; GiB-sized Markov texts come from the GPU generator when a
+    GPU is there (same model and seed on every rank and in the reference arm, so both arms sort the
+    same bytes on the same box)"""
     import numpy as np
     from psascan_b200 import textgen
     gen, kw, dsize, mb, _ = WORKLOADS[workload]
     n = size or dsize
     kw = dict(kw)
-    kw["seed"] = kw.get("seed", 0) + 1000 * rank
+    source = "numpy"
     if gen == "random" and n >= (1 << 26):
-        # fast path for big uniform texts: raw generator bytes folded into 0..254
         rng = np.random.default_rng(kw["seed"])
         t = rng.integers(0, 255, size=n, dtype=np.uint8)
-        return t, (mb if mb < n else 0)
-    if gen == "markov" and n >= (1 << 26):
+    elif gen == "markov" and n >= (1 << 26) and _cuda_ok():
+        t = textgen.markov_torch(n, seed=kw["seed"]).cpu().numpy()
+        source = "torch-cuda"
+    else:
+        t = textgen.GENERATORS[gen](n, **kw)
+    return t, (mb if mb < n else 0), source
+
+
+def _cuda_ok():
+    try:
         import torch
-        if torch.cuda.is_available():   # GiB-sized Markov texts are generated on the GPU (same model)
-            return textgen.markov_torch(n, seed=kw["seed"]).cpu().numpy(), (mb if mb < n else 0)
-    return textgen.GENERATORS[gen](n, **kw), (mb if mb < n else 0)
+        return torch.cuda.is_available()
+    except Exception:
+        return False
 
 
 class ClockSampler:
@@ -106,27 +129,197 @@ def measured_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def run_reference_sample(text, threads, mem="8gi"):
-    """times oracle/_ref/construct_sa (the unmodified reference, libsais variant) on `text`."""
+def host_threads():
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
+def mem_available_bytes():
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                return int(line.split()[1]) * 1024
+    except OSError:
+        pass
+    return 8 << 30
+
+
+def reference_budget(n, threads, n_blocks=1):
+    """(-m bytes, threads) for the reference: 14 MiB of its budget go to every thread and a block takes
+    5.2 bytes per symbol (psascan.hpp:73-91).  n_blocks == 1: the largest budget the host allows (70 % of
+    MemAvailable, the text and the 5n-byte output live in tmpfs beside it); else the budget that cuts the
+    text into n_blocks blocks."""
+    per_thread = 14 << 20
+    if n_blocks > 1:
+        block = -(-n // n_blocks)
+        return int(5.2 * block) + per_thread * threads + (1 << 20), threads
+    avail = mem_available_bytes()
+    budget = int(0.7 * max(0, avail - 6 * n))
+    threads = max(1, min(threads, (budget // 2) // per_thread))
+    return max(budget, per_thread * threads + (64 << 20)), threads
+
+
+def run_reference(text, threads, mem_bytes):
+    """one run of oracle/_ref/construct_sa (the unmodified reference, libsais variant) on `text` in tmpfs;
+    returns (wall seconds, LF steps streamed, seconds inside its streaming phases, its own MiB/s line)"""
     import oracle_lib
     d = tempfile.mkdtemp(prefix="psc_bench_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
     f = os.path.join(d, "t.txt")
     text.tofile(f)
     out = f + ".sa5"
     env = dict(os.environ, OMP_NUM_THREADS=str(threads))
-    t0 = time.perf_counter()
-    subprocess.run([oracle_lib.REF_BIN, f, "-o", out, "-m", mem], check=True, env=env,
-                   stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, stdin=subprocess.DEVNULL)
-    dt = time.perf_counter() - t0
-    for x in os.listdir(d):
-        os.remove(os.path.join(d, x))
-    os.rmdir(d)
-    return dt
+    try:
+        t0 = time.perf_counter()
+        p = subprocess.run([oracle_lib.REF_BIN, f, "-o", out, "-m", str(mem_bytes)], check=True, env=env,
+                           stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, stdin=subprocess.DEVNULL)
+        dt = time.perf_counter() - t0
+    finally:
+        for x in os.listdir(d):
+            os.remove(os.path.join(d, x))
+        os.rmdir(d)
+    # compute_gap.hpp:153-156: "Stream: 100.0%. Time: %.2Lfs. Speed: %.2LfMiB/s" per streaming pass
+    err = p.stderr.decode(errors="replace").replace("\r", "\n")
+    steps, secs = 0.0, 0.0
+    for m in re.finditer(r"Stream: 100\.0%\. Time: ([0-9.]+)s\. Speed: ([0-9.]+)MiB/s", err):
+        tm, sp = float(m.group(1)), float(m.group(2))
+        secs += tm
+        steps += tm * sp * (1 << 20)
+    own = re.search(r"speed: ([0-9.]+)MiB/s", err)
+    blk = re.search(r"Max block size = (\d+)", err)
+    return dt, steps, secs, (float(own.group(1)) if own else None), (int(blk.group(1)) if blk else None)
 
 
-def host_threads():
-    c = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-    return max(1, min(c, 128))  # 14 MiB of budget per thread (psascan.hpp:73-78); 128 keeps -m 8gi valid
+def reference_arm(a, config, n):
+    """--impl reference: the unmodified reference on the SAME full text, all host cores, the largest -m the
+    host allows.  Runs longer than 120 s are timed once, without warm-up (steps_timed says how many)."""
+    text, _, source = gen_text(a.workload, n)
+    cores = host_threads()
+    mem, thr = reference_budget(n, cores)
+    budget_s = 240.0
+    times, info = [], None
+    t_start = time.perf_counter()
+    first = run_reference(text, thr, mem)
+    times.append(first[0])
+    info = first
+    if first[0] <= 120.0:
+        # the first run doubles as the warm-up when there is time for more
+        want = a.steps + (1 if a.warmup > 0 else 0)
+        while len(times) < want and (time.perf_counter() - t_start) + first[0] < budget_s:
+            r = run_reference(text, thr, mem)
+            times.append(r[0])
+            info = r
+        if len(times) > 1 and a.warmup > 0:
+            times = times[1:]
+    sec = sum(times) / len(times)
+    v = n / 1e6 / sec
+    sample = (f"the whole {n}-byte text ({source} generator), construct_sa -m {mem} (libsais build), "
+              f"OMP_NUM_THREADS={thr} of {cores} cores, max block {info[4]}, files in tmpfs")
+    cb = {"value": v, "unit": "MB/s", "cores": thr, "kind": "reference", "sample": sample,
+          "text_bytes_sorted": n, "mem_budget_bytes": mem, "own_speed_mib_s": info[3]}
+    if info[2] > 0:
+        cb["lf_steps_per_s"] = info[1] / info[2]
+    print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": "MB/s",
+                      "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "steps_timed": len(times),
+                      "ms_per_step": sec * 1e3, "higher_is_better": True,
+                      "scaling": "strong" if a.gpus > 1 else "weak", "vs_baseline": None, "dtype": "u8 text, u64 keys, u32 ranks",
+                      "data": "synthetic", "config": dict(config, text_source=source), "cpu_baseline": cb,
+                      "e2e": {"value": v, "unit": "MB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                      "gpu_launches": 0}))
+
+
+def cpu_sample_baseline(text, n_blocks, sample_n):
+    """cpu_baseline leg of the GPU arm: the reference on a bounded prefix of the workload, cut into the same
+    NUMBER of blocks as the GPU run so that its streaming phase (LF steps/s) is exercised too"""
+    cores = host_threads()
+    sample_n = min(len(text), sample_n)
+    mem, thr = reference_budget(sample_n, min(cores, 64), max(1, n_blocks))
+    dt, steps, secs, own, blk = run_reference(text[:sample_n], thr, mem)
+    cb = {"value": sample_n / 1e6 / dt, "unit": "MB/s", "cores": thr, "kind": "reference",
+          "sample": (f"first {sample_n} bytes of the workload, construct_sa -m {mem} (libsais build; max block {blk}: "
+                     f"{n_blocks} blocks like the GPU run), OMP_NUM_THREADS={thr}, tmpfs"),
+          "text_bytes_sorted": sample_n, "seconds": dt}
+    if secs > 0:
+        cb["lf_steps_per_s"] = steps / secs
+        cb["lf_steps"] = steps
+    return cb
+
+
+def walk_roofline(s, r32, peak, peak_src):
+    """roofline of the LF-walk phase (K5 excluded): emit + partition + accumulate kernels, 41.25 algorithmic
+    bytes per step against the random 32-byte sector rate R32 measured in this run"""
+    steps_s = s["lf_steps"] / (s["ms_walk"] / 1e3)
+    roof = {"kernel": "lf_walk_kernel (whole walk phase: rank emit + range partition + gap accumulate)",
+            "bound": "hbm", "unit": "GB/s", "achieved": 41.25 * steps_s / 1e9,
+            "algorithmic_bytes_per_unit": 41.25, "units": "LF steps", "units_per_step": s["lf_steps"],
+            "lf_steps_per_s": steps_s, "ms_walk_per_step": s["ms_walk"],
+            "hbm_copy_peak": peak, "hbm_copy_peak_source": peak_src, "traffic": None}
+    if r32:
+        roof["peak"] = r32
+        roof["peak_source"] = ("R32: independent random 32-byte sector reads over a 16 GiB buffer, full-occupancy grid, "
+                               "measured in this run (psc_bench_random_sectors)")
+        roof["r32_gbs"] = r32
+        roof["steps_per_s_bound"] = r32 * 1e9 / 41.25
+        roof["frac"] = roof["achieved"] / r32
+    else:
+        roof["peak"] = peak
+        roof["peak_source"] = peak_src
+        roof["frac"] = roof["achieved"] / peak
+    return roof
+
+
+def radix_roofline(s, peak, peak_src):
+    gen_ms, gen_b = s["ms_radix_keygen"], s["radix_keygen_bytes"]
+    pair_ms, pair_b = s["ms_radix_pass"] - gen_ms, s["radix_bytes"] - gen_b
+    n_gen = 1 if gen_b else 0
+    launches = max(1, s["radix_passes"] - n_gen * s["n_blocks"])
+    roof = {"kernel": "radix_pass_kernel", "bound": "hbm", "unit": "GB/s",
+            "achieved": pair_b / (pair_ms / 1e3) / 1e9 if pair_ms else None,
+            "algorithmic_bytes_per_unit": 24.0, "units": "(key64,val32) pairs per digit pass (12 B in + 12 B out)",
+            "launches_per_step": launches, "avg_launch_ms": pair_ms / launches,
+            "peak": peak, "peak_source": peak_src, "traffic": None}
+    if gen_b:
+        roof["keygen_pass"] = {"ms": gen_ms, "algorithmic_bytes": gen_b, "GBps": gen_b / (gen_ms / 1e3) / 1e9,
+                               "note": "first pass of round 0: 1 B text in, 12 B out per element"}
+    if roof["achieved"]:
+        roof["frac"] = roof["achieved"] / peak
+    return roof, pair_b, launches
+
+
+def add_traffic(roof, s, pair_b=0, launches=1):
+    """DRAM bytes of one launch from the committed ncu --set full capture (profiles/), scaled to the
+    algorithmic bytes of an average launch of this run"""
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+        key = "lf_walk_kernel" if roof["kernel"].startswith("lf_walk") else "radix_pass_kernel"
+        k = tr[key]
+        units = s["lf_steps"] / max(1, s["n_blocks"] - 1) if key == "lf_walk_kernel" else pair_b / 24.0 / launches
+        roof["traffic"] = k["dram_bytes"] / k["units"] * units
+        roof["traffic_source"] = k["source"]
+        roof["algorithmic_bytes_per_launch"] = roof["algorithmic_bytes_per_unit"] * units
+    except Exception:
+        roof["traffic"] = None
+
+
+def single_block_record(ctx, steps, peak, peak_src):
+    """configs[1] (1 GiB random bytes, one block) kept beside the headline so rounds stay comparable"""
+    import torch
+    text, _, _ = gen_text("random1g", 0)
+    n = len(text)
+    d_text = torch.from_numpy(text).cuda()
+    d_out = torch.empty(5 * n, dtype=torch.uint8, device="cuda")
+    for _ in range(2):
+        ctx.construct_sa_ptr(d_text.data_ptr(), n, d_out.data_ptr(), 0, device=True)
+    st = []
+    for _ in range(max(1, steps)):
+        ctx.construct_sa_ptr(d_text.data_ptr(), n, d_out.data_ptr(), 0, device=True)
+        st.append(ctx.stats())
+    ms = sum(x["ms_total"] for x in st) / len(st)
+    viol = ctx.verify_sa_ptr(d_text.data_ptr(), n, d_out.data_ptr())
+    roof, pair_b, launches = radix_roofline(st[-1], peak, peak_src)
+    add_traffic(roof, st[-1], pair_b, launches)
+    del d_text, d_out
+    torch.cuda.empty_cache()
+    return {"workload": "random1g", "text_bytes": n, "value": n / 1e6 / (ms / 1e3), "unit": "MB/s", "ms_per_step": ms,
+            "steps": len(st), "verified": not any(viol), "roofline": roof}
 
 
 def main():
@@ -134,40 +327,25 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default="random1g", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--size", type=int, default=0)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--cpu-sample", type=int, default=64 << 20, help="bytes of the workload the CPU baseline runs")
+    ap.add_argument("--cpu-sample", type=int, default=64 << 20, help="bytes of the workload the cpu_baseline leg runs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-single-block", action="store_true")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    gen, kw, dsize, _, desc = WORKLOADS[a.workload]
+    gen, kw, dsize, mb_default, desc = WORKLOADS[a.workload]
     n = a.size or dsize
     config = {"workload": a.workload, "description": desc, "text_bytes": n,
-              "l2": "inputs larger than L2 (text + 12 B/suffix sort state >> 126 MB)"}
+              "l2": "inputs larger than L2 (text + 8 B/suffix of block SA and gap arrays >> 126 MB)"}
 
     if a.impl == "reference":
-        if rank != 0:
-            return
-        thr = host_threads()
-        sample_n = min(n, a.cpu_sample)
-        text, _ = gen_text(a.workload, sample_n, 0)
-        for _ in range(min(a.warmup, 1)):
-            run_reference_sample(text, thr)
-        ts = [run_reference_sample(text, thr) for _ in range(a.steps)]
-        sec = sum(ts) / len(ts)
-        v = sample_n / 1e6 / sec
-        cb = {"value": v, "unit": "MB/s", "cores": thr, "kind": "reference",
-              "sample": f"first {sample_n} bytes of the workload, construct_sa -m 8gi (libsais build), tmpfs"}
-        print(json.dumps({"impl": "reference", "metric": "SA construction input MB/s", "value": v, "unit": "MB/s",
-                          "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": sec * 1e3,
-                          "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/u64 keys",
-                          "data": "synthetic", "config": config, "cpu_baseline": cb,
-                          "e2e": {"value": v, "unit": "MB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                          "gpu_launches": 0}))
-        return
+        if rank == 0:
+            reference_arm(a, config, n)
+        return True
 
     import numpy as np
     import torch
@@ -185,24 +363,27 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    text, max_block = gen_text(a.workload, n, rank)
+    text, max_block, source = gen_text(a.workload, n)
+    config["text_source"] = source
     ctx = psascan_b200.Context(local)
-    host_text = torch.from_numpy(text).pin_memory()
-    host_out = torch.empty(5 * n, dtype=torch.uint8).pin_memory()
-    dev_text = host_text.cuda()
-    dev_out = torch.empty(5 * n, dtype=torch.uint8, device="cuda")
-
     sharded = world > 1 and max_block > 0   # multi-block workload: csrc/dist.cu over NCCL (strong scaling)
+    if world > 1 and not sharded:
+        raise SystemExit(f"workload {a.workload} is a single block and does not shard; use --workload {DEFAULT_WORKLOAD}")
+    host_text = torch.from_numpy(text).pin_memory()
+    dev_text = host_text.cuda()
     if sharded:
         from psascan_b200 import dist as pdist
-        if rank != 0:   # every rank must hold the same text
-            text, _ = gen_text(a.workload, n, 0)
-            host_text.copy_(torch.from_numpy(text))
-            dev_text.copy_(host_text)
+        dist.broadcast(dev_text, src=0)   # every rank sorts rank 0's bytes
+        capn = pdist.slice_capacity(ctx, n, world)
+    else:
+        capn = n
+    host_out = torch.empty(5 * capn, dtype=torch.uint8).pin_memory()
+    dev_out = torch.empty(5 * capn, dtype=torch.uint8, device="cuda")
+    share = [0, n]
 
     def step_dev():
         if sharded:   # every rank ends up with its n/world slice of the SA (merge sharded by output range)
-            pdist.construct_sa_slices(ctx, dev_text.data_ptr(), n, dev_out.data_ptr(), max_block)
+            share[0], share[1], _ = pdist.construct_sa_slices(ctx, dev_text.data_ptr(), n, dev_out.data_ptr(), max_block)
         else:
             ctx.construct_sa_ptr(dev_text.data_ptr(), n, dev_out.data_ptr(), max_block, device=True)
         return ctx.stats()
@@ -242,87 +423,92 @@ def main():
     if dist:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     dev_ms, wall_ms, e2e_ms = [float(x) for x in tt.tolist()]
-    ok = True
-    # cheap integrity check of the last result: a permutation checksum
-    sa_sum = int(psascan_b200.lib.decode_sa5(host_out.numpy()[: 5 * min(n, 1 << 20)]).sum()) if n else 0
+
+    # ---- verification of what the timed loops produced (untimed): e2e result and device result
+    step_dev()
+    if sharded:
+        full = torch.empty(5 * n, dtype=torch.uint8, device="cuda") if rank == 0 else None
+        for h in range(world):
+            hb, he = pdist.share_begin(h, n, world), pdist.share_begin(h + 1, n, world)
+            if he <= hb:
+                continue
+            if rank == 0:
+                if h == 0:
+                    full[5 * hb:5 * he].copy_(dev_out[:5 * (he - hb)])
+                else:
+                    dist.recv(full[5 * hb:5 * he], src=h)
+            elif rank == h:
+                dist.send(dev_out[:5 * (he - hb)], dst=0)
+        viol = ctx.verify_sa_ptr(dev_text.data_ptr(), n, full.data_ptr()) if rank == 0 else [0, 0, 0, 0]
+        e2e_same = bool(torch.equal(host_out[:5 * share[1]], dev_out[:5 * share[1]].cpu()))
+        del full
+    else:
+        viol = ctx.verify_sa_ptr(dev_text.data_ptr(), n, dev_out.data_ptr())
+        e2e_same = bool(torch.equal(host_out, dev_out.cpu())) if n <= (1 << 32) else True
+    flag = torch.tensor([0 if (any(viol) or not e2e_same) else 1], device="cuda")
+    if dist:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    verified = bool(flag.item())
+
     if rank == 0:
         s = stats[-1]
-        total_bytes = n if sharded else n * world
-        value = total_bytes * a.steps / 1e6 / (dev_ms / 1e3)
-        e2e = total_bytes * a.steps / 1e6 / (e2e_ms / 1e3)
+        value = n * a.steps / 1e6 / (dev_ms / 1e3)
+        e2e = n * a.steps / 1e6 / (e2e_ms / 1e3)
         peak, peak_src = measured_peaks()
-        if s["lf_steps"] > 0 and s["ms_walk"] > s["ms_radix_pass"]:
-            roof = {"kernel": "lf_walk_kernel", "bound": "hbm", "unit": "GB/s",
-                    "achieved": 41.25 * s["lf_steps"] / (s["ms_walk"] / 1e3) / 1e9,
-                    "algorithmic_bytes_per_unit": 41.25, "units": "LF steps", "peak": peak, "peak_source": peak_src,
-                    "lf_steps_per_s": s["lf_steps"] / (s["ms_walk"] / 1e3), "traffic": None}
-            try:   # random 32-byte sector rate of this GPU (SURVEY 8-d "R32"), the walk's real ceiling
-                r32 = ctx.bench_random_sectors(8 << 30, 128)
-                roof["r32_gbs"] = r32
-                roof["frac_of_r32"] = roof["achieved"] / r32
-            except Exception as e:
-                roof["r32_error"] = str(e)[:100]
-        else:
-            # dominant kernel: the digit pass over (key64, val32) pairs; the one pass per block sort that builds
-            # its keys from the text (8-bit codes) moves fewer bytes and is reported beside it
-            gen_ms, gen_b = s["ms_radix_keygen"], s["radix_keygen_bytes"]
-            pair_ms, pair_b = s["ms_radix_pass"] - gen_ms, s["radix_bytes"] - gen_b
-            n_gen = 1 if gen_b else 0
-            roof = {"kernel": "radix_pass_kernel", "bound": "hbm", "unit": "GB/s",
-                    "achieved": pair_b / (pair_ms / 1e3) / 1e9 if pair_ms else None,
-                    "algorithmic_bytes_per_unit": 24.0, "units": "(key64,val32) pairs per digit pass (12 B in + 12 B out)",
-                    "launches_per_step": s["radix_passes"] - n_gen * s["n_blocks"],
-                    "avg_launch_ms": pair_ms / max(1, s["radix_passes"] - n_gen * s["n_blocks"]),
-                    "peak": peak, "peak_source": peak_src, "traffic": None}
-            if gen_b:
-                roof["keygen_pass"] = {"ms": gen_ms, "algorithmic_bytes": gen_b, "GBps": gen_b / (gen_ms / 1e3) / 1e9,
-                                       "note": "first pass of round 0: 1 B text in, 12 B out per element"}
-        # DRAM bytes of one launch from the committed ncu --set full capture (profiles/), scaled to
-        # the algorithmic bytes of an average launch of this run
-        try:
-            tr = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")))
-            k = tr[roof["kernel"]]
-            if roof["kernel"] == "lf_walk_kernel":
-                units = s["lf_steps"] / max(1, s["n_blocks"] - 1)
-            else:
-                units = pair_b / 24.0 / max(1, roof["launches_per_step"])
-            roof["traffic"] = k["dram_bytes"] / k["units"] * units
-            roof["traffic_source"] = k["source"]
-            roof["algorithmic_bytes_per_launch"] = roof["algorithmic_bytes_per_unit"] * units
-        except Exception:
-            roof["traffic"] = None
-        if roof["achieved"]:
-            roof["frac"] = roof["achieved"] / peak
-        line = {"metric": "SA construction input MB/s", "value": value, "unit": "MB/s", "n_gpus": world,
+        del dev_out, host_out
+        torch.cuda.empty_cache()
+        line = {"metric": METRIC, "value": value, "unit": "MB/s", "n_gpus": world,
                 "steps": a.steps, "warmup": a.warmup, "ms_per_step": dev_ms / a.steps, "higher_is_better": True,
                 "scaling": "strong" if sharded else "weak", "vs_baseline": None,
                 "dtype": "u8 text, u64 keys, u32 ranks", "data": "synthetic",
-                "config": dict(config, parallelism=("block sorts per GPU + sharded tail walk + NCCL all-reduce of gap counts + merge sharded by "
-                                                    "output range (one all-to-all per level); every rank keeps n/N of the SA"
-                                                    if sharded else "replicas" if world > 1 else "single GPU"),
-                               max_block=max_block),
+                "config": dict(config, parallelism=("block sorts per GPU + sharded tail walk + NCCL sum of gap counts + merge "
+                                                    "sharded by output range; every rank keeps n/N of the SA"
+                                                    if sharded else "single GPU"), max_block=max_block, n_blocks=s["n_blocks"]),
                 "clocks": clocks, "wall_ms_per_step": wall_ms / a.steps,
                 "e2e": {"value": e2e, "unit": "MB/s", "h2d_bytes_per_step": n * world if sharded else n,
-                        "d2h_bytes_per_step": 5 * n,
-                        "ms_per_step": e2e_ms / a.steps},
-                "gpu_launches": s["kernel_launches"] * a.steps, "roofline": roof,
+                        "d2h_bytes_per_step": 5 * n, "ms_per_step": e2e_ms / a.steps},
+                "gpu_launches": s["kernel_launches"] * a.steps,
+                "verified": verified, "verify": {"violations": viol, "e2e_equals_device_result": e2e_same,
+                                                 "how": "psc_verify_sa_d: permutation + first-symbol order + tie order via ISA"},
                 "phases_ms": {k: s[k] for k in s if k.startswith("ms_")},
-                "counters": {k: s[k] for k in s if not k.startswith("ms_")}, "sa_checksum_1Mi": sa_sum}
-        if not a.no_cpu_baseline:
-            thr = host_threads()
-            sample_n = min(n, a.cpu_sample)
+                "counters": {k: s[k] for k in s if not k.startswith("ms_")}}
+        if s["lf_steps"] > 0:
+            r32 = None
+            try:   # random 32-byte sector rate of this GPU (SURVEY 8-d "R32"), the walk's ceiling
+                r32 = ctx.bench_random_sectors(16 << 30, 128)
+            except Exception as e:
+                line["r32_error"] = str(e)[:100]
+            # LF steps of the whole job per second of its walk phase (at N > 1: rank 0's share, same wall time)
+            total_steps = sum(max(0, n - min(n, (i + 1) * max_block)) for i in range(s["n_blocks"]))
+            roof = walk_roofline(s, r32, peak, peak_src)
+            add_traffic(roof, s)
+            line["lf_steps_per_s"] = total_steps / (s["ms_walk"] / 1e3)
+            line["lf_steps_per_step"] = total_steps
+            rr, pair_b, launches = radix_roofline(s, peak, peak_src)
+            line["roofline_radix_pass"] = rr
+        else:
+            roof, pair_b, launches = radix_roofline(s, peak, peak_src)
+            add_traffic(roof, s, pair_b, launches)
+        line["roofline"] = roof
+        if world == 1 and not a.no_single_block and a.workload == DEFAULT_WORKLOAD:
             try:
-                sec = run_reference_sample(text[:sample_n], thr)
-                line["cpu_baseline"] = {"value": sample_n / 1e6 / sec, "unit": "MB/s", "cores": thr, "kind": "reference",
-                                        "sample": f"first {sample_n} bytes of the workload, construct_sa -m 8gi (libsais build), tmpfs"}
+                line["single_block"] = single_block_record(ctx, min(a.steps, 3), peak, peak_src)
+                verified = verified and line["single_block"]["verified"]
+                line["verified"] = verified
+            except Exception as e:
+                line["single_block"] = {"error": str(e)[:200]}
+        if world == 1 and not a.no_cpu_baseline:
+            try:
+                line["cpu_baseline"] = cpu_sample_baseline(text, s["n_blocks"], a.cpu_sample)
             except Exception as e:  # the reference binary must travel with the repo
                 line["cpu_baseline"] = {"value": None, "error": str(e)[:200]}
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     ctx.close()
     if dist:
+        dist.barrier()
         dist.destroy_process_group()
-    return ok
+    return verified
 
 
 if __name__ == "__main__":
-    main()
+    sys.exit(0 if main() else 1)

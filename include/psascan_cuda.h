@@ -187,6 +187,12 @@ int psc_copy_h2d(psc_context *ctx, void *dst_d, const void *src, size_t bytes);
 int psc_copy_d2h(psc_context *ctx, void *dst, const void *src_d, size_t bytes);
 int psc_device_info(psc_context *ctx, char *name, size_t name_len, size_t *free_bytes, size_t *total_bytes);
 
+/* O(n) check of a finished suffix array on the device (sufcheck(), extlib/libdivsufsort/lib/utils.c:161-241):
+ * violations[0] = entries >= n, [1] = values that occur twice, [2] = neighbours whose first symbols are out of
+ * order, [3] = neighbours with equal first symbols whose following suffixes are out of order (inverse array).
+ * All four zero <=> out_sa5_d is THE suffix array of text_d.  n < 2^32 - 1 (4 n bytes of scratch). */
+int psc_verify_sa_d(psc_context *ctx, const uint8_t *text_d, long n, const uint8_t *sa5_d, long violations[4]);
+
 /* micro-benchmarks used for the roofline denominators (SURVEY.md 8-d "R32") */
 int psc_bench_random_sectors(psc_context *ctx, size_t bytes, int iters, double *gbs);
 int psc_bench_radix_pass(psc_context *ctx, long n, int iters, double *ms_per_pass);

@@ -179,13 +179,33 @@ double hbm_available(psc_context *ctx) {
 
 static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
                                     uint8_t *out_sa5_d);
+// resident: bytes the caller already holds for this construction (text and output buffers of
+// psc_construct_sa), which must not be charged a second time.  Nothing is trimmed here: unused cached
+// buffers count as available (hbm_available) and are only given back when an allocation fails.
+static long max_block_size_for(psc_context *ctx, long n, double resident) {
+  double avail = psc::hbm_available(ctx) + resident * 0.92;
+  if (avail <= 0) return 0;
+  // single block: text + output + 40 B/symbol of sort state
+  if ((double)n * 52.0 <= avail && n <= (1L << 31) - 4096) return n;
+  // multi block: text n + merged planes 10n + output 5n + gt bits; per block symbol: 40 B sort state,
+  // or sa + gap + bwt + rank planes (<= 255 * 32/224 B) while streaming
+  double per_block = 48.0;
+  // + the rank stream of one walk chunk (2 x 4 B x 2^29 positions at most, walk.cu)
+  double rest = avail - 16.3 * (double)n - 8.0 * (double)std::min(n, 1L << 29);
+  if (rest <= 0) return 0;
+  long mb = (long)(rest / per_block);
+  mb = std::min(mb, (1L << 31) - 4096);
+  mb = std::min(mb, n);
+  return mb / 32 * 32;
+}
+
 
 // PSC_PIPELINE=1: with several blocks the sorts run ahead on a second stream (dist.cu).  Off by default:
 // walk and sort contend for the same HBM, measured 281 ms against 263 ms sequential on 8 x 128 MiB.
 static void construct_sa_device(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
-                                uint8_t *out_sa5_d) {
+                                uint8_t *out_sa5_d, double resident = 0.0) {
   if (n > 0) {
-    if (max_block <= 0) max_block = psc_max_block_size(ctx, n);
+    if (max_block <= 0) max_block = max_block_size_for(ctx, n, resident);
     arg_check(max_block > 0, "text does not fit the HBM budget");
     max_block = std::min(max_block, (1L << 31) - 4096);
     static int pipe = -1;
@@ -205,7 +225,6 @@ static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, lon
   ctx->launches = 0;
   if (n == 0) return;
   PhaseTimer total(ctx, &ctx->stats.ms_total);
-  if (max_block <= 0) max_block = psc_max_block_size(ctx, n);
   arg_check(max_block > 0, "text does not fit the HBM budget");
   max_block = std::min(max_block, (1L << 31) - 4096);
   long B = div_up(n, max_block);
@@ -335,23 +354,7 @@ int psc_shutdown(psc_context *ctx) {
 long psc_max_block_size(psc_context *ctx, long n) {
   if (!ctx || n <= 0) return 0;
   cudaSetDevice(ctx->device);
-  cache_trim(ctx);
-  if (ctx->aux) { cache_trim(ctx->aux); cudaStreamSynchronize(ctx->aux->stream); }
-  cudaStreamSynchronize(ctx->stream);
-  double avail = psc::hbm_available(ctx);
-  if (avail <= 0) return 0;
-  // single block: text + output + 40 B/symbol of sort state
-  if ((double)n * 52.0 <= avail && n <= (1L << 31) - 4096) return n;
-  // multi block: text n + merged planes 10n + output 5n + gt bits; per block symbol: 40 B sort state,
-  // or sa + gap + bwt + rank planes (<= 255 * 32/224 B) while streaming
-  double per_block = 48.0;
-  // + the rank stream of one walk chunk (2 x 4 B x 2^29 positions at most, walk.cu)
-  double rest = avail - 16.3 * (double)n - 8.0 * (double)std::min(n, 1L << 29);
-  if (rest <= 0) return 0;
-  long mb = (long)(rest / per_block);
-  mb = std::min(mb, (1L << 31) - 4096);
-  mb = std::min(mb, n);
-  return mb / 32 * 32;
+  return psc::max_block_size_for(ctx, n, 0.0);
 }
 
 int psc_get_stats(psc_context *ctx, psc_stats *out) {
@@ -378,7 +381,7 @@ int psc_construct_sa(psc_context *ctx, const uint8_t *text, long n, long max_blo
     DevBuf<uint8_t> text_d(ctx, n), out_d(ctx, 5 * (size_t)n);
     double h2d_ms = 0, d2h_ms = 0;
     { PhaseTimer t(ctx, &h2d_ms); h2d(ctx, text_d.p, text, n); }
-    construct_sa_device(ctx, text_d.p, n, max_block, out_d.p);
+    construct_sa_device(ctx, text_d.p, n, max_block, out_d.p, 6.0 * (double)n);  // text + output are ours
     trace_report(ctx);
     { PhaseTimer t(ctx, &d2h_ms); d2h(ctx, out_sa5, out_d.p, 5 * (size_t)n); }
     sync(ctx);

@@ -297,6 +297,9 @@ __global__ void __launch_bounds__(THREADS, MINB)
       lead[j] = 31 - __clz(peers[j]);
       base[j] = 0;
       if (lane == lead[j]) base[j] = atomicAdd(&wh[dgt[c0 + j]], (uint32_t)__popc(peers[j]));
+      // items of one warp with the same digit must take their offsets in item order (stability of the LSD
+      // sort): the leader lanes differ from item to item, so the warp reconverges before the next atomic
+      __syncwarp();
     }
 #pragma unroll
     for (int j = 0; j < CH; ++j) {

@@ -332,3 +332,31 @@ def test_work_guard_subprocess():
     assert "code -5" in r.stdout, (r.stdout, r.stderr[-1500:])
     r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ), capture_output=True, text=True, timeout=600)
     assert "no error" in r.stdout, (r.stdout, r.stderr[-1500:])
+
+
+def test_verify_sa_device(ctx):
+    """psc_verify_sa_d accepts the suffix array and counts each kind of damage (out of range, duplicate,
+    first-symbol order, tie order)."""
+    import torch
+    text = textgen.markov(30000, seed=21)
+    n = len(text)
+    sa5 = ctx.construct_sa(text, max_block=7000)
+    d_text = torch.from_numpy(text).cuda()
+
+    def check(buf):
+        d = torch.from_numpy(buf).cuda()
+        return ctx.verify_sa_ptr(d_text.data_ptr(), n, d.data_ptr())
+
+    assert check(sa5) == [0, 0, 0, 0]
+    sa = decode_sa5(sa5)
+    bad = sa.copy(); bad[100] = n + 5
+    v = check(O.encode_uint40(bad)); assert v[0] == 1
+    bad = sa.copy(); bad[200] = bad[201]
+    v = check(O.encode_uint40(bad)); assert v[1] == 1
+    # swap two neighbours that start with the same symbol: only the tie order is wrong
+    k = next(i for i in range(n - 1) if text[sa[i]] == text[sa[i + 1]])
+    bad = sa.copy(); bad[k], bad[k + 1] = bad[k + 1], bad[k]
+    v = check(O.encode_uint40(bad)); assert v[:2] == [0, 0] and v[3] >= 1
+    k = next(i for i in range(n - 1) if text[sa[i]] != text[sa[i + 1]])
+    bad = sa.copy(); bad[k], bad[k + 1] = bad[k + 1], bad[k]
+    v = check(O.encode_uint40(bad)); assert v[:2] == [0, 0] and v[2] == 1
