@@ -250,8 +250,13 @@ void radix_sort_pairs(psc_context *ctx, uint64_t *keys_a, uint32_t *vals_a, uint
                       const KeyGen *kg = nullptr);
 
 // scan.cu
+// out[0] = 0, out[j] = in[0] + .. + in[j-1] - sub_after_first for j > 0 (the chunk-local merge drops the
+// first `sub_after_first` entries of its first run, see finalmerge.cu)
 void exclusive_scan_u32_to_u64(psc_context *ctx, const uint32_t *in, uint64_t *out, long n,
-                               uint64_t *total_d /* device, may be null */);
+                               uint64_t *total_d /* device, may be null */, uint64_t sub_after_first = 0);
+constexpr int COARSE_TILE = 2048;  // = SCAN_TILE (scan.cu)
+long coarse_carry_tiles(long n);
+void coarse_carries_u32(psc_context *ctx, const uint32_t *in, long n, uint64_t *carry_d /* tiles + 1 */);
 
 // sufsort.cu
 struct BlockSortResult {

@@ -114,7 +114,6 @@ __global__ void merge_bounds_kernel(const uint64_t *__restrict__ E, long m, cons
 }
 
 void merge_gap_scan(psc_context *ctx, const uint32_t *gap_d, long m, uint64_t *E_d) {
-  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
   KTrace kt(ctx, "gap_scan");
   exclusive_scan_u32_to_u64(ctx, gap_d, E_d, m + 1, nullptr);
 }
@@ -129,8 +128,8 @@ void merge_bounds(psc_context *ctx, const uint64_t *E_d, long m, const uint64_t 
   sync(ctx);
 }
 
+// (the callers time the merge phase as a whole: a PhaseTimer synchronises the stream)
 void sa_slice_to_planes(psc_context *ctx, const uint32_t *sa_d, long count, long beg, uint32_t *out_lo, uint8_t *out_hi) {
-  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
   if (count <= 0) return;
   { KTrace kt(ctx, "sa_to_planes"); sa_to_planes_kernel<<<(unsigned)div_up(count, 256), 256, 0, ctx->stream>>>(sa_d, count, (uint64_t)beg, out_lo, out_hi); }
   PSC_LAUNCH_CHECK();
@@ -141,7 +140,6 @@ void sa_slice_to_planes(psc_context *ctx, const uint32_t *sa_d, long count, long
 void merge_level_range(psc_context *ctx, const uint32_t *sa_d, const uint64_t *E_d, long m, long beg,
                        const uint32_t *right_lo, const uint8_t *right_hi, long r_base, long q_beg, long q_end,
                        uint32_t *out_lo, uint8_t *out_hi) {
-  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
   if (q_end <= q_beg) return;
   const long ntiles = div_up(q_end - q_beg, MG_TILE);
   DevBuf<uint32_t> tile_u0(ctx, ntiles);
@@ -166,6 +164,7 @@ void merge_level(psc_context *ctx, const uint32_t *sa_d, const uint32_t *gap_d, 
                  uint32_t *out_lo, uint8_t *out_hi) {
   long total = m + right_len;
   if (total == 0) return;
+  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
   if (right_len == 0) { sa_slice_to_planes(ctx, sa_d, m, beg, out_lo, out_hi); return; }
   DevBuf<uint64_t> E(ctx, m + 1);
   merge_gap_scan(ctx, gap_d, m, E.p);
@@ -200,7 +199,6 @@ __global__ void __launch_bounds__(256)
 }
 
 void pack_sa5(psc_context *ctx, const uint32_t *lo, const uint8_t *hi, long n, uint8_t *out5) {
-  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
   if (n <= 0) return;
   { KTrace kt(ctx, "pack_sa5"); pack_sa5_kernel<<<(unsigned)div_up(div_up(n, 4), 256), 256, 0, ctx->stream>>>(
       lo, hi, n, reinterpret_cast<uint32_t *>(out5), out5); }

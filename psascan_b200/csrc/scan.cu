@@ -7,6 +7,7 @@ namespace psc {
 
 constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_TILE = SC_THREADS * SCAN_ITEMS;
+static_assert(SCAN_TILE == COARSE_TILE, "coarse carries are the scan's tile sums");
 
 __global__ void __launch_bounds__(SC_THREADS)
     scan_reduce_u32_kernel(const uint32_t *__restrict__ in, long n, uint64_t *__restrict__ agg) {
@@ -22,7 +23,7 @@ __global__ void __launch_bounds__(SC_THREADS)
 
 __global__ void __launch_bounds__(SC_THREADS)
     scan_apply_u32_kernel(const uint32_t *__restrict__ in, long n, const uint64_t *__restrict__ agg,
-                          uint64_t *__restrict__ out) {
+                          uint64_t *__restrict__ out, uint64_t sub_after_first) {
   __shared__ uint64_t sm[SC_THREADS / 32 + 1];
   long base = (long)blockIdx.x * SCAN_TILE + (long)threadIdx.x * SCAN_ITEMS;
   uint32_t v[SCAN_ITEMS];
@@ -33,7 +34,7 @@ __global__ void __launch_bounds__(SC_THREADS)
   uint64_t ex = block_excl_sum<uint64_t>(s, sm, &tot) + agg[blockIdx.x];
 #pragma unroll
   for (int k = 0; k < SCAN_ITEMS; ++k) {
-    if (base + k < n) out[base + k] = ex;
+    if (base + k < n) out[base + k] = (base + k > 0) ? ex - sub_after_first : ex;
     ex += v[k];
   }
 }
@@ -98,8 +99,20 @@ void scan_aggregates_sum(psc_context *ctx, uint64_t *agg_d, long n, uint64_t *to
   PSC_LAUNCH_CHECK();
   ctx->launches++;
 }
+// carry[j] = sum of in[0 .. j * SCAN_TILE) for j in [0, tiles), carry[tiles] = sum of everything
+// (tiles = ceil(n / SCAN_TILE)): the coarse level of a two-level search in the scanned array
+long coarse_carry_tiles(long n) { return div_up(n, (long)SCAN_TILE); }
+void coarse_carries_u32(psc_context *ctx, const uint32_t *in, long n, uint64_t *carry_d) {
+  const long tiles = coarse_carry_tiles(n);
+  if (tiles <= 0) { PSC_CUDA(cudaMemsetAsync(carry_d, 0, 8, ctx->stream)); return; }
+  scan_reduce_u32_kernel<<<(unsigned)tiles, SC_THREADS, 0, ctx->stream>>>(in, n, carry_d);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
+  scan_aggregates_sum(ctx, carry_d, tiles, carry_d + tiles);
+}
+
 void exclusive_scan_u32_to_u64(psc_context *ctx, const uint32_t *in, uint64_t *out, long n,
-                               uint64_t *total_d) {
+                               uint64_t *total_d, uint64_t sub_after_first) {
   if (n <= 0) {
     if (total_d) PSC_CUDA(cudaMemsetAsync(total_d, 0, 8, ctx->stream));
     return;
@@ -109,7 +122,7 @@ void exclusive_scan_u32_to_u64(psc_context *ctx, const uint32_t *in, uint64_t *o
   scan_reduce_u32_kernel<<<(unsigned)tiles, SC_THREADS, 0, ctx->stream>>>(in, n, agg.p);
   PSC_LAUNCH_CHECK();
   scan_aggregates_sum(ctx, agg.p, tiles, total_d);
-  scan_apply_u32_kernel<<<(unsigned)tiles, SC_THREADS, 0, ctx->stream>>>(in, n, agg.p, out);
+  scan_apply_u32_kernel<<<(unsigned)tiles, SC_THREADS, 0, ctx->stream>>>(in, n, agg.p, out, sub_after_first);
   PSC_LAUNCH_CHECK();
   ctx->launches += 2;
 }
