@@ -193,6 +193,19 @@ int psc_device_info(psc_context *ctx, char *name, size_t name_len, size_t *free_
  * All four zero <=> out_sa5_d is THE suffix array of text_d.  n < 2^32 - 1 (4 n bytes of scratch). */
 int psc_verify_sa_d(psc_context *ctx, const uint8_t *text_d, long n, const uint8_t *sa5_d, long violations[4]);
 
+/* The same check for callers that must not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The scratch (inverse array + counters) is a static device array inside the library, 16 MiB + 256
+ * bytes that every GPU loading the library holds until the process exits; the call issues no cudaMalloc /
+ * cudaFree / allocating library routine.  n <= PSC_VERIFY_NOALLOC_MAX_N (= psc_verify_noalloc_max_n()), larger
+ * inputs are rejected with PSC_EARG.  All calls share the scratch: it is cleared at the start of every call,
+ * and calls that overlap on the GPU (other streams or threads) race -- serialise them.  Same arguments and
+ * results as psc_verify_sa_d. */
+#define PSC_VERIFY_NOALLOC_MAX_N 4194304L
+long psc_verify_noalloc_max_n(void);
+int psc_verify_sa_noalloc_d(psc_context *ctx, const uint8_t *text_d, long n, const uint8_t *sa5_d,
+                            long violations[4]);
+
 /* micro-benchmarks used for the roofline denominators (SURVEY.md 8-d "R32") */
 int psc_bench_random_sectors(psc_context *ctx, size_t bytes, int iters, double *gbs);
 int psc_bench_radix_pass(psc_context *ctx, long n, int iters, double *ms_per_pass);

@@ -68,3 +68,65 @@ extern "C" int psc_verify_sa_d(psc_context *ctx, const uint8_t *text_d, long n, 
     return PSC_OK;
   } catch (const CudaError &e) { return e.code; }
 }
+
+// ---- the same check without any allocation ---------------------------------------------------------------
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+// it): the inverse-array scratch of the check lives in a file-scope device array of fixed size, which
+// every GPU that loads the library holds until the process exits (16 MiB + 256 bytes).  No counterpart
+// in the reference.
+//   * every call shares the array: calls that overlap on the GPU (other streams, other threads) race;
+//   * the array keeps the last call's contents: the part a call uses is cleared first.
+constexpr long VERIFY_NOALLOC_MAX = PSC_VERIFY_NOALLOC_MAX_N;
+static __device__ __align__(256) uint32_t g_verify_scratch[64 + VERIFY_NOALLOC_MAX];  // [0, 64): counters
+
+namespace {
+constexpr int MAX_DEVICES = 64;
+std::mutex g_scratch_mu;
+uint32_t *g_scratch_addr[MAX_DEVICES] = {nullptr};
+
+// device address of the scratch on the CURRENT device, looked up once per device (in host code the
+// array's name is only a stand-in for it)
+uint32_t *scratch_on_device(int device) {
+  if (device < 0 || device >= MAX_DEVICES) { set_error("psc_verify_sa_noalloc_d: device %d out of range", device); throw CudaError{PSC_EARG}; }
+  std::lock_guard<std::mutex> lk(g_scratch_mu);
+  if (!g_scratch_addr[device]) {
+    void *p = nullptr;
+    PSC_CUDA(cudaGetSymbolAddress(&p, g_verify_scratch));
+    g_scratch_addr[device] = static_cast<uint32_t *>(p);
+  }
+  return g_scratch_addr[device];
+}
+}  // namespace
+
+extern "C" long psc_verify_noalloc_max_n(void) { return VERIFY_NOALLOC_MAX; }
+
+extern "C" int psc_verify_sa_noalloc_d(psc_context *ctx, const uint8_t *text_d, long n, const uint8_t *sa5_d,
+                                       long violations[4]) {
+  try {
+    if (!ctx || n < 0 || !violations || (n > 0 && (!text_d || !sa5_d))) {
+      set_error("psc_verify_sa_noalloc_d: bad argument");
+      return PSC_EARG;
+    }
+    if (n > VERIFY_NOALLOC_MAX) {
+      set_error("psc_verify_sa_noalloc_d: n = %ld exceeds the static scratch (at most %ld entries); use psc_verify_sa_d",
+                n, VERIFY_NOALLOC_MAX);
+      return PSC_EARG;
+    }
+    for (int k = 0; k < 4; ++k) violations[k] = 0;
+    if (n == 0) return PSC_OK;
+    PSC_CUDA(cudaSetDevice(ctx->device));
+    uint32_t *base = scratch_on_device(ctx->device);
+    unsigned long long *viol = reinterpret_cast<unsigned long long *>(base);
+    uint32_t *isa = base + 64;
+    PSC_CUDA(cudaMemsetAsync(base, 0, (size_t)(64 + n) * 4, ctx->stream));  // what the last call left behind
+    verify_scatter_kernel<<<(unsigned)div_up(n, 256), 256, 0, ctx->stream>>>(sa5_d, n, isa, viol);
+    PSC_LAUNCH_CHECK();
+    verify_order_kernel<<<(unsigned)div_up(n, 256), 256, 0, ctx->stream>>>(text_d, sa5_d, n, isa, viol);
+    PSC_LAUNCH_CHECK();
+    unsigned long long h[4];
+    PSC_CUDA(cudaMemcpyAsync(h, viol, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    PSC_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < 4; ++k) violations[k] = (long)h[k];
+    return PSC_OK;
+  } catch (const CudaError &e) { return e.code; }
+}

@@ -14,6 +14,7 @@ EXPORTS = [
     "psc_bench_random_sectors", "psc_bench_radix_pass", "psc_device_alloc", "psc_device_free",
     "psc_pinned_alloc", "psc_pinned_free", "psc_copy_h2d", "psc_copy_d2h", "psc_device_info", "psc_construct_sa_dist_d",
     "psc_construct_sa_dist_slice_d", "psc_dist_slice_capacity", "psc_verify_sa_d",
+    "psc_verify_sa_noalloc_d", "psc_verify_noalloc_max_n",
 ]
 
 
@@ -231,6 +232,13 @@ class Context:
         """O(n) device check (psc_verify_sa_d): returns the four violation counts, all zero for a correct SA"""
         v = (C.c_long * 4)()
         self._chk(self.lib.psc_verify_sa_d(self.h, C.c_void_p(text_dev_ptr), C.c_long(n), C.c_void_p(sa5_dev_ptr), v))
+        return [int(x) for x in v]
+
+    def verify_sa_noalloc_ptr(self, text_dev_ptr, n, sa5_dev_ptr):
+        """psc_verify_sa_noalloc_d: the same check with the library's static scratch (no allocation, n bounded)"""
+        v = (C.c_long * 4)()
+        self._chk(self.lib.psc_verify_sa_noalloc_d(self.h, C.c_void_p(text_dev_ptr), C.c_long(n),
+                                                   C.c_void_p(sa5_dev_ptr), v))
         return [int(x) for x in v]
 
     def bench_random_sectors(self, nbytes, iters=256):
