@@ -2,6 +2,7 @@
 #include <stdarg.h>
 #include <algorithm>
 #include "common.cuh"
+#include "finalmerge.cuh"
 
 namespace psc {
 
@@ -124,7 +125,6 @@ void *cache_alloc(psc_context *ctx, size_t bytes) {
   if (e == cudaErrorMemoryAllocation) {  // unused size classes (of either context) hold the memory
     cudaGetLastError();
     cache_trim(ctx);
-    if (ctx->aux) cache_trim(ctx->aux);
     cudaDeviceSynchronize();
     e = cudaMallocAsync(&q, cls, ctx->stream);
   }
@@ -171,56 +171,96 @@ double hbm_available(psc_context *ctx) {
   uint64_t reserved = 0, used = 0;
   cudaMemPoolGetAttribute(ctx->pool, cudaMemPoolAttrReservedMemCurrent, &reserved);
   cudaMemPoolGetAttribute(ctx->pool, cudaMemPoolAttrUsedMemCurrent, &used);
-  double avail = (double)free_b + (double)(reserved - used) + (double)ctx->cache_free_bytes +
-                 (ctx->aux ? (double)ctx->aux->cache_free_bytes : 0.0);
+  double avail = (double)free_b + (double)(reserved - used) + (double)ctx->cache_free_bytes;
   if (ctx->hbm_budget && (double)ctx->hbm_budget < avail) avail = (double)ctx->hbm_budget;
   return avail * 0.92;
 }
 
+// the text of block `id` is complete in HBM (psc_construct_sa copies it block by block on the side stream)
+struct BlockGate {
+  virtual void wait(psc_context *ctx, long id) const = 0;
+  virtual ~BlockGate() {}
+};
 static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
-                                    uint8_t *out_sa5_d);
-// resident: bytes the caller already holds for this construction (text and output buffers of
-// psc_construct_sa), which must not be charged a second time.  Nothing is trimmed here: unused cached
-// buffers count as available (hbm_available) and are only given back when an allocation fails.
-static long max_block_size_for(psc_context *ctx, long n, double resident) {
-  double avail = psc::hbm_available(ctx) + resident * 0.92;
+                                    uint8_t *out_sa5_d, const ChunkSink *sink, const BlockGate *gate);
+// Largest block for a text of n symbols.  io_bytes: text and output buffers the caller has NOT allocated yet
+// (the public query: 6n); the construction entry points size the blocks after their I/O buffers exist,
+// so those are never charged twice.  Nothing is trimmed here: unused cached buffers count as available
+// (hbm_available) and are only given back to the driver when an allocation fails.
+static long max_block_size_for(psc_context *ctx, long n, double io_bytes) {
+  double avail = psc::hbm_available(ctx) - io_bytes;
   if (avail <= 0) return 0;
-  // single block: text + output + 40 B/symbol of sort state
-  if ((double)n * 52.0 <= avail && n <= (1L << 31) - 4096) return n;
-  // multi block: text n + merged planes 10n + output 5n + gt bits; per block symbol: 40 B sort state,
-  // or sa + gap + bwt + rank planes (<= 255 * 32/224 B) while streaming
-  double per_block = 48.0;
-  // + the rank stream of one walk chunk (2 x 4 B x 2^29 positions at most, walk.cu)
-  double rest = avail - 16.3 * (double)n - 8.0 * (double)std::min(n, 1L << 29);
+  // single block: 40 B/symbol of sort state (keys, values, SA)
+  if ((double)n * 40.0 <= avail && n <= (1L << 31) - 4096) return n;
+  // several blocks: every block's SA and gap array stay until the final merge (8n), gt bits (n/4), the merge
+  // scratch of one output chunk (planes + scanned gaps: 18 B per slot), the rank stream of one walk chunk
+  // (2 x 4 B x 2^29 positions at most, walk.cu); per block symbol 40 B of sort state, or BWT + rank planes
+  // (<= 255 * 32/224 B) while streaming
+  const double chunk = (double)std::min(n, merge_chunk_entries());
+  double rest = avail - 8.3 * (double)n - 18.0 * chunk - 8.0 * (double)std::min(n, 1L << 29);
   if (rest <= 0) return 0;
-  long mb = (long)(rest / per_block);
+  long mb = (long)(rest / 40.0);
   mb = std::min(mb, (1L << 31) - 4096);
   mb = std::min(mb, n);
   return mb / 32 * 32;
 }
 
-
-// PSC_PIPELINE=1: with several blocks the sorts run ahead on a second stream (dist.cu).  Off by default:
-// walk and sort contend for the same HBM, measured 281 ms against 263 ms sequential on 8 x 128 MiB.
-static void construct_sa_device(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
-                                uint8_t *out_sa5_d, double resident = 0.0) {
-  if (n > 0) {
-    if (max_block <= 0) max_block = max_block_size_for(ctx, n, resident);
-    arg_check(max_block > 0, "text does not fit the HBM budget");
-    max_block = std::min(max_block, (1L << 31) - 4096);
-    static int pipe = -1;
-    if (pipe < 0) { const char *e = getenv("PSC_PIPELINE"); pipe = e ? atoi(e) : 0; }
-    if (pipe && div_up(n, max_block) > 1) {
-      // sorted-ahead blocks (2 x 5.2 B) + one block in the sorter (40 B) + one streaming (<= 45 B per symbol)
-      double need = 16.3 * (double)n + 8.0 * (double)std::min(n, 1L << 29) + 96.0 * (double)max_block;
-      if (need <= hbm_available(ctx)) { construct_sa_pipelined(ctx, text_d, n, max_block, out_sa5_d); return; }
-    }
-  }
-  construct_sa_sequential(ctx, text_d, n, max_block, out_sa5_d);
+static long choose_max_block(psc_context *ctx, long n, long max_block) {
+  if (n <= 0) return 1;
+  if (max_block <= 0) max_block = max_block_size_for(ctx, n, 0.0);
+  arg_check(max_block > 0, "text does not fit the HBM budget");
+  return std::min(max_block, (1L << 31) - 4096);
 }
 
+static void construct_sa_device(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
+                                uint8_t *out_sa5_d) {
+  construct_sa_sequential(ctx, text_d, n, choose_max_block(ctx, n, max_block), out_sa5_d, nullptr, nullptr);
+}
+
+// ---- host buffers in and out: copies overlapped with the pipeline on the side stream ------------------
+// Text: block by block, right to left (the order the pipeline consumes it), one event per block.
+struct H2DGate : BlockGate {
+  std::vector<cudaEvent_t> ev;
+  void wait(psc_context *ctx, long id) const override {
+    PSC_CUDA(cudaStreamWaitEvent(ctx->stream, ev[id], 0));
+  }
+  ~H2DGate() { for (auto e : ev) if (e) cudaEventDestroy(e); }
+};
+// Output: finished chunks are packed into one of two device buffers and leave by D2H on the side stream
+// while the next chunk is merged; no 5n-byte output buffer exists on the device.
+struct HostSink : ChunkSink {
+  uint8_t *host_out = nullptr;
+  mutable DevBuf<uint8_t> buf[2];
+  mutable cudaEvent_t packed[2] = {nullptr, nullptr}, copied[2] = {nullptr, nullptr};
+  mutable bool busy[2] = {false, false};
+  HostSink(psc_context *ctx, uint8_t *out, long chunk_entries) : host_out(out) {
+    for (int k = 0; k < 2; ++k) {
+      buf[k].alloc(ctx, (size_t)chunk_entries * 5 + 64);
+      PSC_CUDA(cudaEventCreateWithFlags(&packed[k], cudaEventDisableTiming));
+      PSC_CUDA(cudaEventCreateWithFlags(&copied[k], cudaEventDisableTiming));
+    }
+  }
+  uint8_t *buffer(psc_context *ctx, int chunk, long) const override {
+    const int k = chunk & 1;
+    if (busy[k]) PSC_CUDA(cudaStreamWaitEvent(ctx->stream, copied[k], 0));  // its last copy must have left
+    return buf[k].p;
+  }
+  void done(psc_context *ctx, int chunk, long first_entry, long entries) const override {
+    const int k = chunk & 1;
+    PSC_CUDA(cudaEventRecord(packed[k], ctx->stream));
+    PSC_CUDA(cudaStreamWaitEvent(ctx->side, packed[k], 0));
+    PSC_CUDA(cudaMemcpyAsync(host_out + 5 * (size_t)first_entry, buf[k].p, 5 * (size_t)entries, cudaMemcpyDeviceToHost, ctx->side));
+    PSC_CUDA(cudaEventRecord(copied[k], ctx->side));
+    busy[k] = true;
+  }
+  void finish(psc_context *ctx) const { PSC_CUDA(cudaStreamSynchronize(ctx->side)); }
+  ~HostSink() {
+    for (int k = 0; k < 2; ++k) { if (packed[k]) cudaEventDestroy(packed[k]); if (copied[k]) cudaEventDestroy(copied[k]); }
+  }
+};
+
 static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
-                                    uint8_t *out_sa5_d) {
+                                    uint8_t *out_sa5_d, const ChunkSink *sink, const BlockGate *gate) {
   memset(&ctx->stats, 0, sizeof(ctx->stats));
   ctx->launches = 0;
   if (n == 0) return;
@@ -231,19 +271,17 @@ static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, lon
   ctx->stats.n_blocks = B;
   long gwords = (n + 1 + 31) / 32 + 2;
   DevBuf<uint32_t> Ga, Gb;
-  DevBuf<uint32_t> Mlo[2];
-  DevBuf<uint8_t> Mhi[2];
   if (B > 1) {
     Ga.alloc(ctx, gwords); Gb.alloc(ctx, gwords);
     Ga.zero(); Gb.zero();
-    for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); if (need_hi_plane(n)) Mhi[k].alloc(ctx, n);  /* high bytes only above 4 GiB */ }
   }
+  // every block's SA and gap array stay until the final merge (8 bytes per suffix), finalmerge.cu
+  std::vector<DevBuf<uint32_t>> sa(B), gap(B);
   uint32_t *gt_cur = Ga.p, *gt_new = Gb.p;
-  int cur = 0;
-  long right_len = 0;
   for (long id = B - 1; id >= 0; --id) {
     long beg = id * max_block, end = std::min(n, beg + max_block), m = end - beg, t = n - end;
     const uint8_t *block_d = text_d + beg, *after_d = text_d + end;
+    if (gate) gate->wait(ctx, id);  // the block's text is on its way from the host (side stream)
     BlockSortResult res;
     {
       DevBuf<uint32_t> gt_end;
@@ -261,26 +299,38 @@ static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, lon
       }
     }
     res.isa.release();
-    DevBuf<uint32_t> gap;
     if (t > 0) {
-      gap.alloc(ctx, m + 1);
-      gap.zero();
+      gap[id].alloc(ctx, m + 1);
+      gap[id].zero();
       gap_of_block(ctx, block_d, m, res.sa.p, res.i0, after_d, t, gt_cur, end, id > 0 ? gt_new : nullptr,
-                   gap.p);
+                   gap[id].p);
     }
-    if (B == 1) {  // one piece: the block SA goes straight to the 40-bit writer
-      pack_sa5_from_sa(ctx, res.sa.p, n, 0, out_sa5_d);
-      sync(ctx);
-      ctx->stats.kernel_launches = ctx->launches;
-      return;
-    }
-    int nxt = 1 - cur;
-    merge_level(ctx, res.sa.p, gap.p, m, beg, Mlo[cur].p, Mhi[cur].p, right_len, Mlo[nxt].p, Mhi[nxt].p);
-    cur = nxt;
-    right_len += m;
+    sa[id] = std::move(res.sa);
     std::swap(gt_cur, gt_new);
   }
-  pack_sa5(ctx, Mlo[cur].p, Mhi[cur].p, n, out_sa5_d);
+  Ga.release(); Gb.release();
+  if (B == 1) {  // one piece: the block SA goes straight to the 40-bit writer
+    if (sink) {
+      const long C = merge_chunk_entries();
+      PhaseTimer timer(ctx, &ctx->stats.ms_merge);
+      for (long a = 0, i = 0; a < n; a += C, ++i) {
+        const long cnt = std::min(C, n - a);
+        pack_sa5_from_sa(ctx, sa[0].p + a, cnt, 0, sink->buffer(ctx, (int)i, cnt), false);
+        sink->done(ctx, (int)i, a, cnt);
+      }
+    } else {
+      pack_sa5_from_sa(ctx, sa[0].p, n, 0, out_sa5_d);
+    }
+  } else {
+    std::vector<MergePiece> pc(B);
+    for (long id = 0; id < B; ++id) {
+      pc[id].beg = id * max_block;
+      pc[id].m = std::min(n, pc[id].beg + max_block) - pc[id].beg;
+      pc[id].sa = sa[id].p;
+      pc[id].gap = gap[id].p;
+    }
+    final_merge_resident(ctx, pc, n, out_sa5_d, sink);
+  }
   sync(ctx);
   ctx->stats.kernel_launches = ctx->launches;
 }
@@ -335,14 +385,6 @@ int psc_shutdown(psc_context *ctx) {
   if (!ctx) return PSC_OK;
   cudaSetDevice(ctx->device);
   cache_trim(ctx);
-  if (ctx->aux) {
-    cache_trim(ctx->aux);
-    cudaStreamSynchronize(ctx->aux->stream);
-    cudaStreamDestroy(ctx->aux->stream);
-    cudaStreamDestroy(ctx->aux->side);
-    delete ctx->aux;
-    ctx->aux = nullptr;
-  }
   cudaStreamSynchronize(ctx->stream);
   cudaMemPoolTrimTo(ctx->pool, 0);
   cudaStreamDestroy(ctx->stream);
@@ -354,7 +396,7 @@ int psc_shutdown(psc_context *ctx) {
 long psc_max_block_size(psc_context *ctx, long n) {
   if (!ctx || n <= 0) return 0;
   cudaSetDevice(ctx->device);
-  return psc::max_block_size_for(ctx, n, 0.0);
+  return psc::max_block_size_for(ctx, n, 6.0 * (double)n);
 }
 
 int psc_get_stats(psc_context *ctx, psc_stats *out) {
@@ -378,15 +420,33 @@ int psc_construct_sa(psc_context *ctx, const uint8_t *text, long n, long max_blo
     arg_check(ctx && n >= 0 && (n == 0 || (text && out_sa5)), "psc_construct_sa");
     if (n == 0) return;
     PSC_CUDA(cudaSetDevice(ctx->device));
-    DevBuf<uint8_t> text_d(ctx, n), out_d(ctx, 5 * (size_t)n);
-    double h2d_ms = 0, d2h_ms = 0;
-    { PhaseTimer t(ctx, &h2d_ms); h2d(ctx, text_d.p, text, n); }
-    construct_sa_device(ctx, text_d.p, n, max_block, out_d.p, 6.0 * (double)n);  // text + output are ours
+    DevBuf<uint8_t> text_d(ctx, n);
+    const long C = merge_chunk_entries();
+    HostSink sink(ctx, out_sa5, std::min(n, C));
+    max_block = choose_max_block(ctx, n, max_block);
+    const long B = div_up(n, max_block);
+    // the side stream must not start before earlier work on the main stream that used these buffers is done
+    cudaEvent_t start;
+    PSC_CUDA(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
+    PSC_CUDA(cudaEventRecord(start, ctx->stream));
+    PSC_CUDA(cudaStreamWaitEvent(ctx->side, start, 0));
+    cudaEventDestroy(start);
+    H2DGate gate;
+    gate.ev.assign(B, nullptr);
+    for (long id = B - 1; id >= 0; --id) {
+      const long beg = id * max_block, end = std::min(n, beg + max_block);
+      PSC_CUDA(cudaMemcpyAsync(text_d.p + beg, text + beg, (size_t)(end - beg), cudaMemcpyHostToDevice, ctx->side));
+      PSC_CUDA(cudaEventCreateWithFlags(&gate.ev[id], cudaEventDisableTiming));
+      PSC_CUDA(cudaEventRecord(gate.ev[id], ctx->side));
+    }
+    try {
+      construct_sa_sequential(ctx, text_d.p, n, max_block, nullptr, &sink, &gate);
+    } catch (...) {  // the side stream may still be writing into buffers this frame owns
+      cudaStreamSynchronize(ctx->side);
+      throw;
+    }
+    sink.finish(ctx);
     trace_report(ctx);
-    { PhaseTimer t(ctx, &d2h_ms); d2h(ctx, out_sa5, out_d.p, 5 * (size_t)n); }
-    sync(ctx);
-    ctx->stats.ms_h2d = h2d_ms;
-    ctx->stats.ms_d2h = d2h_ms;
   });
 }
 

@@ -342,7 +342,7 @@ void merge_level_range(psc_context *ctx, const uint32_t *sa_d, const uint64_t *E
                        const uint32_t *right_lo, const uint8_t *right_hi, long r_base, long q_beg, long q_end,
                        uint32_t *out_lo, uint8_t *out_hi);
 void pack_sa5(psc_context *ctx, const uint32_t *lo, const uint8_t *hi, long n, uint8_t *out5);
-void pack_sa5_from_sa(psc_context *ctx, const uint32_t *sa, long n, long beg, uint8_t *out5);
+void pack_sa5_from_sa(psc_context *ctx, const uint32_t *sa, long n, long beg, uint8_t *out5, bool timed = true);
 void unpack_sa5(psc_context *ctx, const uint8_t *in5, long n, uint32_t *lo, uint8_t *hi);
 void gap_to_bitvector(psc_context *ctx, const uint32_t *gap_l, long len_l, long len_r,
                       uint32_t *bv_words);

@@ -234,9 +234,14 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-void pack_sa5_from_sa(psc_context *ctx, const uint32_t *sa, long n, long beg, uint8_t *out5) {
-  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
+static void pack_sa5_from_sa_launch(psc_context *ctx, const uint32_t *sa, long n, long beg, uint8_t *out5);
+void pack_sa5_from_sa(psc_context *ctx, const uint32_t *sa, long n, long beg, uint8_t *out5, bool timed) {
   if (n <= 0) return;
+  if (!timed) { pack_sa5_from_sa_launch(ctx, sa, n, beg, out5); return; }
+  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
+  pack_sa5_from_sa_launch(ctx, sa, n, beg, out5);
+}
+static void pack_sa5_from_sa_launch(psc_context *ctx, const uint32_t *sa, long n, long beg, uint8_t *out5) {
   { KTrace kt(ctx, "pack_sa32"); pack_sa32_kernel<<<(unsigned)div_up(div_up(n, 4), 256), 256, 0, ctx->stream>>>(
       sa, n, (uint64_t)beg, reinterpret_cast<uint32_t *>(out5), out5); }
   PSC_LAUNCH_CHECK();

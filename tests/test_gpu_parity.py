@@ -290,24 +290,34 @@ def test_dist_schedule_single_rank(ctx):
             assert np.array_equal(d_out.cpu().numpy(), sa5), (name, mb)
 
 
-def test_pipelined_schedule_subprocess():
-    """PSC_PIPELINE=1 (block sorts running ahead on a second stream, csrc/dist.cu) is read once per
-    process, so it is exercised in a child: every multi-block golden case must come out bit-exact."""
+@pytest.mark.parametrize("env", [dict(PSC_WALK_MODE="1"), dict(PSC_WALK_MODE="2"), dict(PSC_WALK_CHUNK="4096"),
+                                 dict(PSC_WALKERS="7"), dict(PSC_MERGE_CHUNK="1000"),
+                                 dict(PSC_MERGE_CHUNK="64", PSC_WALK_CHUNK="2048", PSC_WALK_MODE="2")],
+                         ids=["walk_warp_aggregated", "walk_emit_partition", "walk_multi_chunk", "seven_walkers",
+                              "merge_small_chunks", "all_small"])
+def test_env_selected_paths_subprocess(env):
+    """Paths chosen by environment variables read once per process (the warp-aggregated and the
+    emit + partition walk, tails cut into several walk chunks, a handful of walkers, the final merge in
+    many small output chunks) run in a child: every multi-block golden case must come out bit-exact,
+    through the host-buffer entry point (overlapped copies) and the device-buffer one."""
     import os, subprocess, sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     code = (
-        "import sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import sys, numpy as np, torch; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
         "import psascan_b200 as P\n"
         "from golden_cases import golden_cases, golden_text\n"
         "c = P.Context(0)\n"
         "for name, gen, kw, n, sa5 in golden_cases():\n"
         "    t = golden_text(gen, kw, n)\n"
+        "    dt = torch.from_numpy(t).cuda(); do = torch.zeros(5 * n, dtype=torch.uint8, device='cuda')\n"
         "    for mb in (n // 3 + 1, 1000):\n"
         "        assert np.array_equal(c.construct_sa(t, max_block=mb), sa5), (name, mb)\n"
-        "print('pipelined ok', c.stats()['n_blocks'])\n" % (root, os.path.join(root, "tests")))
-    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, PSC_PIPELINE="1"),
-                       capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0 and "pipelined ok" in r.stdout, r.stderr[-2000:]
+        "        do.zero_(); c.construct_sa_ptr(dt.data_ptr(), n, do.data_ptr(), mb, device=True)\n"
+        "        assert np.array_equal(do.cpu().numpy(), sa5), (name, mb, 'device')\n"
+        "print('paths ok', c.stats()['n_blocks'])\n" % (root, os.path.join(root, "tests")))
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, **env),
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0 and "paths ok" in r.stdout, r.stderr[-2000:]
 
 
 def test_work_guard_subprocess():
