@@ -374,6 +374,7 @@ def main():
     if sharded:
         from psascan_b200 import dist as pdist
         dist.broadcast(dev_text, src=0)   # every rank sorts rank 0's bytes
+        pdist.init(ctx)                   # NCCL communicator inside the library (csrc/comm.cu)
         capn = pdist.slice_capacity(ctx, n, world)
     else:
         capn = n
@@ -409,6 +410,7 @@ def main():
     barrier()
     wall = time.perf_counter() - t0
     dev_ms = sum(s["ms_total"] for s in stats)
+    comm = dict(pdist.comm_stats(ctx), nranks=world, backend="NCCL inside the library (csrc/comm.cu)") if sharded else None
     # end to end through the host-buffer entry point
     step_e2e()
     barrier()
@@ -461,13 +463,13 @@ def main():
                 "steps": a.steps, "warmup": a.warmup, "ms_per_step": dev_ms / a.steps, "higher_is_better": True,
                 "scaling": "strong" if sharded else "weak", "vs_baseline": None,
                 "dtype": "u8 text, u64 keys, u32 ranks", "data": "synthetic",
-                "config": dict(config, parallelism=("block sorts per GPU + sharded tail walk + NCCL sum of gap counts + merge "
-                                                    "sharded by output range; every rank keeps n/N of the SA"
+                "config": dict(config, parallelism=("block sorts per GPU + sharded tail walk + ncclReduceScatter of gap counts + ONE exchange of SA/gap slices, "
+                                                    "merge by output range; every rank keeps n/N of the SA"
                                                     if sharded else "single GPU"), max_block=max_block, n_blocks=s["n_blocks"]),
                 "clocks": clocks, "wall_ms_per_step": wall_ms / a.steps,
                 "e2e": {"value": e2e, "unit": "MB/s", "h2d_bytes_per_step": n * world if sharded else n,
                         "d2h_bytes_per_step": 5 * n, "ms_per_step": e2e_ms / a.steps},
-                "gpu_launches": s["kernel_launches"] * a.steps,
+                "gpu_launches": s["kernel_launches"] * a.steps, "comm_per_step": comm,
                 "verified": verified, "verify": {"violations": viol, "e2e_equals_device_result": e2e_same,
                                                  "how": "psc_verify_sa_d: permutation + first-symbol order + tie order via ISA"},
                 "phases_ms": {k: s[k] for k in s if k.startswith("ms_")},
@@ -503,6 +505,8 @@ def main():
             except Exception as e:  # the reference binary must travel with the repo
                 line["cpu_baseline"] = {"value": None, "error": str(e)[:200]}
         print(json.dumps(line), flush=True)
+    if sharded:
+        pdist.finalize(ctx)
     ctx.close()
     if dist:
         dist.barrier()

@@ -130,39 +130,33 @@ int psc_construct_sa(psc_context *ctx, const uint8_t *text, long n, long max_blo
 int psc_construct_sa_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
                        uint8_t *out_sa5_d);
 
-/* ---- the same over several GPUs, one process per GPU.  Blocks are sorted on
- * separate GPUs (rank r owns blocks B-1-r, B-1-r-world, ...), every GPU walks a contiguous share of
- * the tail against a replicated rank structure, per-GPU gap counts are summed.  The collectives
- * are delegated to the caller (NCCL through torch.distributed in psascan_b200/dist.py):
- *   fn(user, PSC_COLL_BCAST, buf_d, bytes, root)           broadcast buf_d from rank `root`
- *   fn(user, PSC_COLL_ALLREDUCE_SUM_U32, buf_d, bytes, 0)  element-wise uint32 sum over all ranks
- *   fn(user, PSC_COLL_ALLTOALLV, args, bytes, 0)           args = psc_alltoallv_args* (HOST memory): rank r
- *                                                          sends send_bytes[h] consecutive bytes of send_d to every
- *                                                          rank h (in rank order) and receives recv_bytes[h] from
- *                                                          it into recv_d (in rank order); bytes = total received
- * fn must return 0 after the operation has COMPLETED on the device.  Every rank passes the whole text.
- * The merge (merge.hpp:54-180) is sharded by output range: after each level a rank holds an n/world
- * slice of the merged sequence and fetches the slice of the previous level it needs with one all-to-all.
+/* ---- the same over several GPUs, one rank per GPU; the reference is single-process, so
+ * nothing in it corresponds.  Ranks may be processes (torchrun) or threads of one process (host/psascan.hpp);
+ * each creates its own context with psc_init(device) and joins with psc_dist_init.  NCCL (libnccl.so.2,
+ * opened at run time) carries every collective, enqueued on the library's stream: no callbacks.
+ *   psc_dist_unique_id   rank 0 creates the 128-byte id (ncclGetUniqueId) and hands it to the other ranks
+ *                        by any means (torch.distributed, MPI, a shared variable)
+ *   psc_dist_init        collective: ncclCommInitRank on the context's device; world == 1 needs no id
+ *   psc_dist_finalize    destroys the communicator (psc_shutdown does not)
+ * Schedule (csrc/dist.cu): blocks are sorted on separate GPUs (rank r owns blocks B-1-r, B-1-r-world, ...);
+ * per block the owner broadcasts the BWT, gt bits and the walkers' start ranks (the block SA stays with its
+ * owner), every GPU walks a contiguous share of the tail against the replicated rank structure, the per-GPU
+ * gap counts are summed with ncclReduceScatter, new gt bits are all-gathered; the merge (merge.hpp:54-180)
+ * is sharded by OUTPUT range after ONE exchange of SA and gap slices.  Every rank passes the whole text.
+ *   psc_construct_sa_dist_slice_d  every rank keeps its slice: entries [*slice_beg, *slice_beg + *slice_len)
+ *                                  of the SA as 5-byte values in out_slice_sa5_d, which must hold
+ *                                  psc_dist_slice_capacity(n, world) entries
  *   psc_construct_sa_dist_d        every rank receives the whole suffix array (slices broadcast at the end)
- *   psc_construct_sa_dist_slice_d  every rank keeps its slice: entries [*slice_beg, *slice_beg + *slice_len) of
- *                                  the SA as 5-byte values in out_slice_sa5_d, which must hold
- *                                  psc_dist_slice_capacity(n, world) entries */
-#define PSC_COLL_BCAST 1
-#define PSC_COLL_ALLREDUCE_SUM_U32 2
-#define PSC_COLL_ALLTOALLV 3
-typedef struct psc_alltoallv_args {
-  const void *send_d;
-  void *recv_d;
-  const size_t *send_bytes; /* [world] */
-  const size_t *recv_bytes; /* [world] */
-} psc_alltoallv_args;
-typedef int (*psc_collective_fn)(void *user, int op, void *buf_d, size_t bytes, int root);
-int psc_construct_sa_dist_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
-                            uint8_t *out_sa5_d, int rank, int world, psc_collective_fn fn, void *user);
+ * A context that never called psc_dist_init is a world of one. */
+int psc_dist_unique_id(uint8_t id[128]);
+int psc_dist_init(psc_context *ctx, const uint8_t id[128], int rank, int world);
+int psc_dist_finalize(psc_context *ctx);
+int psc_construct_sa_dist_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block, uint8_t *out_sa5_d);
 int psc_construct_sa_dist_slice_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
-                                  uint8_t *out_slice_sa5_d, long *slice_beg, long *slice_len, int rank, int world,
-                                  psc_collective_fn fn, void *user);
+                                  uint8_t *out_slice_sa5_d, long *slice_beg, long *slice_len);
 long psc_dist_slice_capacity(long n, int world);
+/* collectives issued by the last distributed construction of this rank and the bytes they moved */
+int psc_dist_stats(psc_context *ctx, long *n_collectives, double *bytes);
 
 /* per-phase device time (ms, CUDA events) and counters of the last psc_construct_sa* call */
 typedef struct psc_stats {

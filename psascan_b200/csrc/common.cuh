@@ -35,8 +35,11 @@ static inline bool need_hi_plane(long n) { return n > (1L << 32) || getenv("PSC_
 
 }  // namespace psc
 
+namespace psc { struct Comm; }
+
 struct psc_context {
   int device = 0;
+  psc::Comm *comm = nullptr;  // psc_dist_init (comm.cu): this context is one rank of a multi-GPU construction
   int n_sm = 148;
   size_t hbm_budget = 0;
   cudaStream_t stream = nullptr;
@@ -59,8 +62,6 @@ struct psc_context {
   std::vector<CacheBlock> cache;
   size_t cache_free_bytes = 0;
   std::mutex cache_mu;  // buffers of the sorter context are released by the streaming thread
-  // second context (own stream, own cache) on which block sorts run ahead of the walk/merge chain
-  psc_context *aux = nullptr;
   int walk_threads_per_sm = 512;  // measured on 8 x 128 MiB: 512 -> 98 ms, 1024 -> 111, 2048 -> 104, 256 -> 123
 };
 
@@ -321,9 +322,15 @@ void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, con
              const uint64_t *start_rank_d, const uint32_t *gt_in_bits_d, long gt_in_off,
              uint32_t *gt_out_bits_d, long gt_out_off, uint32_t *gap_d);
 
-// dist.cu: single-GPU schedule with the block sorts running ahead on a second stream
-void construct_sa_pipelined(psc_context *ctx, const uint8_t *text_d, long n, long max_block, uint8_t *out_sa5_d);
-
+// walkers over a range of tail positions (walk.cu)
+struct WalkPlan {
+  std::vector<uint64_t> b;     // W + 1 boundaries, tail-relative
+  std::vector<long> chunk_at;  // walker index at which every chunk starts, then W
+};
+void make_walk_plan(psc_context *ctx, long lo, long hi, WalkPlan *p);
+void walk_with_plan(psc_context *ctx, const psc_rank *rk, long i0, uint8_t last, const uint64_t *Cmap,
+                    const uint8_t *after_d, const WalkPlan &p, const uint64_t *b_d, const uint64_t *sr_d,
+                    const uint32_t *gt_cur, long gt_off, uint32_t *gt_new, uint32_t *gap_d);
 // K5 + K6 over tail positions [lo, hi), chunked (walk.cu)
 void walk_tail_range(psc_context *ctx, const psc_rank *rk, long i0, uint8_t last, const uint64_t *Cmap,
                      const uint8_t *block_d, const uint32_t *sa_d, long m, const uint8_t *after_d, long t,

@@ -1,25 +1,28 @@
-// dist.cu -- the block pipeline over several GPUs, one process per GPU.
+// dist.cu -- the block pipeline over several GPUs, one rank per GPU, NCCL over NVLink.
 //
 //   phase 1  block sorts are independent once gt_end is computed by plain text comparison past the
-//            block end (no gt bits of the next block needed), so rank r sorts blocks B-1-r, B-1-r-N, ...
-//   phase 2  blocks right to left: the owner broadcasts SA, BWT and gt_begin bits of the block;
-//            every rank builds the rank structure, walks ITS contiguous share of the tail
-//            (compute_gap.hpp:68-69 splits the tail over threads the same way), and the per-GPU
-//            gap counts and gt bits are summed over NCCL.  The merge is sharded by OUTPUT range:
-//            after every level rank g holds slots [g*L/G, (g+1)*L/G) of the merged sequence (L = its
-//            length so far); the entries of the previous level it needs form one contiguous range,
-//            known to every rank from the scanned gap array alone, and arrive by one all-to-all.
-//            Nothing of size n lives on a GPU except the text: planes and output are n/G per rank.
-// Collectives are delegated to the caller through psc_collective_fn (torch.distributed in
-// psascan_b200/dist.py, NCCL over NVLink); the library synchronises its stream around them.
+//            block end (no gt bits of the next block needed): rank r sorts blocks B-1-r, B-1-r-N, ...
+//            and keeps their SA; BWT, gt_begin bits and i0 wait for phase 2.
+//   phase 2  blocks right to left.  The owner computes the start ranks of ALL ranks' walkers (K5 needs
+//            the block SA, which never leaves its owner) and broadcasts [start ranks | gt_begin bits |
+//            BWT]: m bytes + a few MB instead of the 5m of round 1.  Every rank builds the rank
+//            structure, walks ITS share of the tail (compute_gap.hpp:68-69 cuts the tail over threads
+//            the same way; shares begin on 32-bit word boundaries of the gt bit array), then
+//              ncclReduceScatter(sum, uint32) of the gap counts: every rank keeps a 1/N slice per block,
+//              ncclAllGather of the new gt words (disjoint word ranges, no reduction).
+//   phase 3  the N-way merge by output range (finalmerge.cu): rank g produces output slots
+//            [g n/N, (g+1) n/N).  The split of every boundary over the blocks is a distributed search
+//            (each rank searches its gap slices, one small all-reduce per block), then ONE exchange
+//            brings every rank the slices of every block's SA and gap array its range needs
+//            (8 n/N bytes per rank), and the cascade runs locally.  Nothing of size n lives on a GPU
+//            except the text.
+// All collectives are enqueued on the context's stream (comm.cu); the host only waits where it needs
+// a value (block meta data, split tables).
 #include <algorithm>
-#include <condition_variable>
-#include <deque>
 #include <memory>
-#include <mutex>
 #include <string>
-#include <thread>
-#include "common.cuh"
+#include "comm.cuh"
+#include "finalmerge.cuh"
 
 namespace psc {
 
@@ -49,6 +52,7 @@ struct OwnedBlock {
 };
 
 struct BlockMeta { long long i0; int end_bit; int last; };
+constexpr size_t META_BYTES = 256;
 
 // K0 (by plain comparison past the block end) + block sort + gt_begin bits + BWT of text[beg, end):
 // everything a block contributes that does not depend on the blocks to its right.
@@ -81,40 +85,52 @@ static std::unique_ptr<OwnedBlock> sort_owned_block(psc_context *ctx, const uint
   return ob;
 }
 
-static void coll(psc_context *ctx, psc_collective_fn fn, void *user, int op, void *buf, size_t bytes, int root) {
-  sync(ctx);
-  if (fn(user, op, buf, bytes, root) != 0) {
-    set_error("collective callback failed (op %d, %zu bytes)", op, bytes);
-    throw CudaError{PSC_ECUDA};
-  }
-}
-
 // first output slot of rank g when `len` slots are shared out: equal shares rounded up to a multiple of 4
 // (the 40-bit writer packs 4 entries into 5 aligned words)
 static long share_begin(long g, long len, int world) {
   long per = (div_up(len, (long)world) + 3) / 4 * 4;
   return std::min(len, per * g);
 }
-long share_begin_public(long g, long len, int world) { return share_begin(g, len, world); }
-static size_t overlap(long a0, long a1, long b0, long b1) {
+static long overlap_lo(long a0, long b0) { return std::max(a0, b0); }
+static long overlap_len(long a0, long a1, long b0, long b1) {
   long lo = std::max(a0, b0), hi = std::min(a1, b1);
-  return hi > lo ? (size_t)(hi - lo) : 0;
+  return hi > lo ? hi - lo : 0;
 }
 
-// gather == true: out_sa5_d[5n] receives the whole SA on every rank (slices broadcast at the end);
-// else out_sa5_d receives this rank's slice only: entries [*slice_beg, *slice_beg + *slice_len).
-void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max_block, uint8_t *out_sa5_d,
-                       int rank, int world, psc_collective_fn fn, void *user, bool gather, long *slice_beg,
-                       long *slice_len) {
-  memset(&ctx->stats, 0, sizeof(ctx->stats));
-  ctx->launches = 0;
-  if (n == 0) return;
-  PhaseTimer total(ctx, &ctx->stats.ms_total);
-  max_block = std::min(max_block, (1L << 31) - 4096);
-  const long B = div_up(n, max_block);
-  ctx->stats.n_blocks = B;
+// rank g's share of the tail of a block ending at text position `end`: the walkers of [lo, hi) write the gt
+// bits with indices [end + lo, end + hi), and shares are cut on 32-bit word boundaries of that bit array so
+// that the new words of all ranks are disjoint (all-gather, no reduction)
+struct TailShares {
+  long wl = 0, per_w = 0;  // first word touched, words per rank
+  std::vector<long> lo;    // world + 1 tail-relative boundaries
+};
+static TailShares tail_shares(long end, long n, int world) {
+  TailShares s;
+  s.wl = end >> 5;
+  const long wh = (n - 1) >> 5;
+  s.per_w = div_up(wh - s.wl + 1, (long)world);
+  s.lo.resize(world + 1);
+  for (int g = 0; g <= world; ++g) {
+    long bit = std::min(n, std::max(end, 32 * (s.wl + g * s.per_w)));
+    s.lo[g] = bit - end;
+  }
+  return s;
+}
+
+struct DistPieces {  // what a rank keeps of every block until the final merge
+  std::vector<DevBuf<uint32_t>> sa;       // whole SA of the blocks this rank owns
+  std::vector<DevBuf<uint32_t>> gap;      // this rank's slice of every block's summed gap array
+  std::vector<DevBuf<uint64_t>> carry;    // coarse carries of that slice
+  std::vector<long> per;                  // slice length (entries per rank) of every block
+};
+
+// phases 1 and 2; fills `pcs`, totals_d[g * B + id] = sum of rank g's gap slice of block id
+static void dist_blocks(psc_context *ctx, Comm &cm, const uint8_t *text_d, long n, long max_block, long B,
+                        DistPieces &pcs, DevBuf<uint64_t> &totals_d) {
+  const int rank = cm.rank, world = cm.world;
   auto owner = [&](long id) { return (int)((B - 1 - id) % world); };
   auto bounds = [&](long id, long *beg, long *end) { *beg = id * max_block; *end = std::min(n, *beg + max_block); };
+  pcs.sa.resize(B); pcs.gap.resize(B); pcs.carry.resize(B); pcs.per.assign(B, 0);
 
   // ---- phase 1: my blocks, independent of each other
   std::vector<std::unique_ptr<OwnedBlock>> mine(B);
@@ -126,82 +142,90 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
   }
 
   // ---- phase 2: right to left
-  const long gwords = (n + 1 + 31) / 32 + 2;
+  const long gwords = (n + 1 + 31) / 32 + 2 + world + 2;
   DevBuf<uint32_t> Ga(ctx, gwords), Gb(ctx, gwords);
   Ga.zero(); Gb.zero();
   uint32_t *gt_cur = Ga.p, *gt_new = Gb.p;
-  // my share of the merged sequence (double buffered) and what arrives from the other ranks per level
-  const bool hi_plane = need_hi_plane(n);  // high bytes only above 4 GiB
-  const long cap = share_begin(1, n, world) + 16;
-  DevBuf<uint32_t> Mlo[2], Rlo;
-  DevBuf<uint8_t> Mhi[2], Rhi;
-  for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, cap); if (hi_plane) Mhi[k].alloc(ctx, cap); }
-  if (world > 1) { Rlo.alloc(ctx, cap); if (hi_plane) Rhi.alloc(ctx, cap); }
-  int cur = 0;
-  long right_len = 0;
+  totals_d.alloc(ctx, (size_t)B * world);
+  totals_d.zero();
+  DevBuf<uint64_t> my_tot(ctx, B);
+  my_tot.zero();
   for (long id = B - 1; id >= 0; --id) {
     long beg, end;
     bounds(id, &beg, &end);
     const long m = end - beg, t = n - end;
     const int own = owner(id);
     OwnedBlock *ob = mine[id].get();
-    // one broadcast per block: [meta | SA | gt_begin bits | BWT] packed into one buffer (every collective
-    // costs a stream synchronisation and a host round trip)
-    DevBuf<uint8_t> pack;
-    uint32_t *sa_p, *gtb_p;
-    uint8_t *bwt_p = nullptr;
-    BlockMeta meta{0, 0, 0};
-    if (world == 1) {
-      sa_p = ob->sa.p; gtb_p = ob->gtb.p; bwt_p = ob->bwt.p;
-      meta = BlockMeta{ob->i0, ob->end_bit, (int)ob->last};
-    } else {
-      const size_t sa_off = 256, gtb_off = sa_off + (((size_t)m * 4 + 255) & ~(size_t)255);
-      const size_t gtb_bytes = (size_t)(m / 32 + 2) * 4;
-      const size_t bwt_off = gtb_off + ((gtb_bytes + 255) & ~(size_t)255);
-      const size_t total = bwt_off + (t > 0 ? (size_t)m : 0);
-      pack.alloc(ctx, total);
-      sa_p = reinterpret_cast<uint32_t *>(pack.p + sa_off);
-      gtb_p = reinterpret_cast<uint32_t *>(pack.p + gtb_off);
-      if (t > 0) bwt_p = pack.p + bwt_off;
-      if (own == rank) {
-        meta = BlockMeta{ob->i0, ob->end_bit, (int)ob->last};
-        h2d(ctx, reinterpret_cast<BlockMeta *>(pack.p), &meta, 1);
-        PSC_CUDA(cudaMemcpyAsync(sa_p, ob->sa.p, (size_t)m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
-        PSC_CUDA(cudaMemcpyAsync(gtb_p, ob->gtb.p, gtb_bytes, cudaMemcpyDeviceToDevice, ctx->stream));
-        if (t > 0) PSC_CUDA(cudaMemcpyAsync(bwt_p, ob->bwt.p, (size_t)m, cudaMemcpyDeviceToDevice, ctx->stream));
-        sync(ctx);          // `meta` is a stack variable
-        mine[id].reset();   // the packed copy is what the rest of the level uses
+    // walkers of every rank (the same plan on every rank: it only depends on t, world and the SM count)
+    TailShares sh;
+    std::vector<WalkPlan> plans(world);
+    std::vector<long> off(world + 1, 0);
+    if (t > 0) {
+      sh = tail_shares(end, n, world);
+      for (int g = 0; g < world; ++g) {
+        if (sh.lo[g + 1] > sh.lo[g]) make_walk_plan(ctx, sh.lo[g], sh.lo[g + 1], &plans[g]);
+        off[g + 1] = off[g] + (long)plans[g].b.size();
       }
-      coll(ctx, fn, user, PSC_COLL_BCAST, pack.p, total, own);
-      d2h(ctx, &meta, reinterpret_cast<BlockMeta *>(pack.p), 1);
-      sync(ctx);
     }
+    const long nbnd = off[world];
+    // one broadcast per block: [meta | walker boundaries' ranks | gt_begin bits | BWT]
+    const size_t sr_off = META_BYTES, sr_bytes = ((size_t)nbnd * 8 + 255) & ~(size_t)255;
+    const size_t gtb_off = sr_off + sr_bytes, gtb_bytes = (size_t)(m / 32 + 2) * 4;
+    const size_t bwt_off = gtb_off + ((gtb_bytes + 255) & ~(size_t)255);
+    const size_t total = bwt_off + (t > 0 ? (size_t)m : 0);
+    DevBuf<uint8_t> pack(ctx, total);
+    uint64_t *sr_p = reinterpret_cast<uint64_t *>(pack.p + sr_off);
+    uint32_t *gtb_p = reinterpret_cast<uint32_t *>(pack.p + gtb_off);
+    uint8_t *bwt_p = t > 0 ? pack.p + bwt_off : nullptr;
+    DevBuf<uint64_t> b_d(ctx, std::max(1L, nbnd));
+    if (nbnd > 0) {
+      std::vector<uint64_t> all_b((size_t)nbnd);
+      for (int g = 0; g < world; ++g) std::copy(plans[g].b.begin(), plans[g].b.end(), all_b.begin() + off[g]);
+      h2d(ctx, b_d.p, all_b.data(), all_b.size());
+      sync(ctx);  // all_b is a local vector
+    }
+    BlockMeta meta{0, 0, 0};
+    if (own == rank) {
+      meta = BlockMeta{ob->i0, ob->end_bit, (int)ob->last};
+      h2d(ctx, reinterpret_cast<BlockMeta *>(pack.p), &meta, 1);
+      // K5 for everybody's walkers: the rank of suffix(end + b) among the block's suffixes
+      if (nbnd > 0)
+        initial_ranks(ctx, text_d + beg, ob->sa.p, m, text_d + end, t, 1, gt_cur, end, nbnd, b_d.p, sr_p);
+      PSC_CUDA(cudaMemcpyAsync(gtb_p, ob->gtb.p, gtb_bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+      if (t > 0) PSC_CUDA(cudaMemcpyAsync(bwt_p, ob->bwt.p, (size_t)m, cudaMemcpyDeviceToDevice, ctx->stream));
+      sync(ctx);  // `meta` is a stack variable
+      pcs.sa[id] = std::move(ob->sa);
+      mine[id].reset();  // BWT and bits now live in the packed copy
+    }
+    cm.bcast(ctx, pack.p, total, own);
+    if (world > 1) { d2h(ctx, &meta, reinterpret_cast<BlockMeta *>(pack.p), 1); sync(ctx); }
     const long i0 = (long)meta.i0;
     PSC_CUDA(cudaMemsetAsync(gt_new, 0, gwords * 4, ctx->stream));
-    DevBuf<uint32_t> gap;
     if (t > 0) {
-      gap.alloc(ctx, m + 1 + (world > 1 ? (n >> 5) + 2 - ((end - 1) >> 5) : 0));
-      gap.zero();
+      const long per = (div_up(m + 1, (long)world) + 3) / 4 * 4;
+      pcs.per[id] = per;
+      DevBuf<uint32_t> gap_full(ctx, (size_t)per * world);
+      gap_full.zero();
       psc_rank *rk = rank_build(ctx, bwt_p, m, i0);
       try {
         uint64_t Cmap[256], run = 0;
         for (int c = 0; c < 256; ++c) { Cmap[c] = run; run += (uint64_t)rk->counts[c] + (c == meta.last ? 1 : 0); }
-        // my contiguous share of the tail, boundaries on multiples of 32
-        long per = div_up(div_up(t, (long)world), 32) * 32;
-        long lo = std::min(t, per * rank), hi = std::min(t, per * (rank + 1));
-        if (hi > lo)
-          walk_tail_range(ctx, rk, i0, (uint8_t)meta.last, Cmap, text_d + beg, sa_p, m, text_d + end, t, lo, hi, gt_cur,
-                          end, id > 0 ? gt_new : nullptr, gap.p);
+        const WalkPlan &p = plans[rank];
+        if (p.b.size() > 1)  // walker k of my plan starts from the rank of boundary k + 1
+          walk_with_plan(ctx, rk, i0, (uint8_t)meta.last, Cmap, text_d + end, p, b_d.p + off[rank], sr_p + off[rank] + 1,
+                         gt_cur, end, id > 0 ? gt_new : nullptr, gap_full.p);
       } catch (...) { rank_free(rk); throw; }
       rank_free(rk);
-      if (world > 1) {
-        // gap counts and (disjoint bits of disjoint tail ranges: SUM == OR) the new gt bits in ONE all-reduce:
-        // the gt words ride behind the gap array
-        const long w0 = (end - 1) >> 5, w1 = (n >> 5) + 1, gw = id > 0 ? w1 - w0 : 0;
-        if (gw) PSC_CUDA(cudaMemcpyAsync(gap.p + m + 1, gt_new + w0, (size_t)gw * 4, cudaMemcpyDeviceToDevice, ctx->stream));
-        coll(ctx, fn, user, PSC_COLL_ALLREDUCE_SUM_U32, gap.p, (size_t)(m + 1 + gw) * 4, 0);
-        if (gw) PSC_CUDA(cudaMemcpyAsync(gt_new + w0, gap.p + m + 1, (size_t)gw * 4, cudaMemcpyDeviceToDevice, ctx->stream));
-      }
+      // per-GPU gap counts summed, every rank keeps a slice
+      pcs.gap[id].alloc(ctx, per);
+      cm.reduce_scatter_u32(ctx, gap_full.p, pcs.gap[id].p, (size_t)per);
+      const long cnt = std::max(0L, std::min(per, m + 1 - per * rank));
+      pcs.carry[id].alloc(ctx, coarse_carry_tiles(cnt) + 1);
+      coarse_carries_u32(ctx, pcs.gap[id].p, cnt, pcs.carry[id].p);
+      PSC_CUDA(cudaMemcpyAsync(my_tot.p + id, pcs.carry[id].p + coarse_carry_tiles(cnt), 8, cudaMemcpyDeviceToDevice, ctx->stream));
+      // new gt words of disjoint word ranges
+      if (id > 0 && world > 1)
+        cm.allgather(ctx, gt_new + sh.wl + sh.per_w * rank, gt_new + sh.wl, (size_t)sh.per_w * 4);
     }
     if (id > 0) {
       if (m > 1) {
@@ -211,256 +235,252 @@ void construct_sa_dist(psc_context *ctx, const uint8_t *text_d, long n, long max
       if (meta.end_bit) { set_bit_kernel<<<1, 1, 0, ctx->stream>>>(gt_new, end - 1); PSC_LAUNCH_CHECK(); }
       ctx->launches += 2;
     }
-    int nxt = 1 - cur;
-    {
-      const long R = right_len, L = R + m;
-      const long a = share_begin(rank, L, world), b = share_begin(rank + 1, L, world);
-      if (R == 0) {
-        sa_slice_to_planes(ctx, sa_p + a, b - a, beg, Mlo[nxt].p, Mhi[nxt].p);
-      } else {
-        DevBuf<uint64_t> E(ctx, m + 1);
-        merge_gap_scan(ctx, gap.p, m, E.p);
-        if (world == 1) {
-          merge_level_range(ctx, sa_p, E.p, m, beg, Mlo[cur].p, Mhi[cur].p, 0, 0, L, Mlo[nxt].p, Mhi[nxt].p);
-        } else {
-          // output slot Q[g] is preceded by cnt[g] block suffixes, hence by ra[g] = Q[g] - cnt[g] entries of the
-          // right side: rank g needs entries [ra[g], ra[g+1]) of the previous level, held in shares P[.]
-          std::vector<uint64_t> Q(world + 1), cnt(world + 1);
-          std::vector<long> ra(world + 1), P(world + 1);
-          for (int g = 0; g <= world; ++g) { Q[g] = (uint64_t)share_begin(g, L, world); P[g] = share_begin(g, R, world); }
-          merge_bounds(ctx, E.p, m, Q.data(), world + 1, cnt.data());
-          for (int g = 0; g <= world; ++g) ra[g] = (long)(Q[g] - cnt[g]);
-          std::vector<size_t> sb(world), rb(world), sb4(world), rb4(world);
-          size_t rtot = 0;
-          for (int h = 0; h < world; ++h) {
-            sb[h] = overlap(P[rank], P[rank + 1], ra[h], ra[h + 1]);
-            rb[h] = overlap(P[h], P[h + 1], ra[rank], ra[rank + 1]);
-            sb4[h] = sb[h] * 4; rb4[h] = rb[h] * 4;
-            rtot += rb[h];
-          }
-          if ((long)rtot != ra[rank + 1] - ra[rank] || (long)rtot > cap) { set_error("sharded merge: inconsistent exchange plan"); throw CudaError{PSC_EARG}; }
-          psc_alltoallv_args x{Mlo[cur].p, Rlo.p, sb4.data(), rb4.data()};
-          coll(ctx, fn, user, PSC_COLL_ALLTOALLV, &x, rtot * 4, 0);
-          if (hi_plane) {
-            psc_alltoallv_args y{Mhi[cur].p, Rhi.p, sb.data(), rb.data()};
-            coll(ctx, fn, user, PSC_COLL_ALLTOALLV, &y, rtot, 0);
-          }
-          merge_level_range(ctx, sa_p, E.p, m, beg, Rlo.p, Rhi.p, ra[rank], a, b, Mlo[nxt].p, Mhi[nxt].p);
+    std::swap(gt_cur, gt_new);
+  }
+  // slice totals of all ranks
+  if (world > 1) cm.allgather(ctx, my_tot.p, totals_d.p, (size_t)B * 8);
+  else PSC_CUDA(cudaMemcpyAsync(totals_d.p, my_tot.p, (size_t)B * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+  sync(ctx);
+}
+
+// ---- phase 3: the merge by output range ---------------------------------------------------------------
+// Boundaries: rank g's output range [share_begin(g), share_begin(g+1)) cut into chunks of
+// merge_chunk_entries(); bd = all boundaries in order, first[g] = index of rank g's first one.
+static void dist_merge(psc_context *ctx, Comm &cm, long n, long max_block, long B, DistPieces &pcs,
+                       DevBuf<uint64_t> &totals_d, uint8_t *out_slice5_d) {
+  PhaseTimer timer(ctx, &ctx->stats.ms_merge);
+  const int rank = cm.rank, world = cm.world;
+  auto owner = [&](long id) { return (int)((B - 1 - id) % world); };
+  auto blen = [&](long id) { return std::min(n, (id + 1) * max_block) - id * max_block; };
+  const long C = merge_chunk_entries();
+  std::vector<uint64_t> bd;
+  std::vector<int> first(world + 1);
+  for (int g = 0; g < world; ++g) {
+    first[g] = (int)bd.size();
+    for (long a = share_begin(g, n, world); a < share_begin(g + 1, n, world); a += C) bd.push_back((uint64_t)a);
+  }
+  first[world] = (int)bd.size();
+  bd.push_back((uint64_t)n);
+  const int nb = (int)bd.size();
+  std::vector<uint64_t> tot((size_t)B * world);
+  d2h(ctx, tot.data(), totals_d.p, tot.size());
+  sync(ctx);
+  // split: level by level, every rank answers from its gap slices, answers are summed
+  MergePlan plan;
+  plan.resize((int)B, nb);
+  {
+    KTrace kt(ctx, "merge_split");
+    DevBuf<uint64_t> tab(ctx, (size_t)3 * B * nb);
+    uint64_t *Qd = tab.p, *UEd = tab.p + (size_t)B * nb;  // U and E of one level are adjacent: one all-reduce
+    h2d(ctx, Qd, bd.data(), nb);
+    for (long k = 0; k < B; ++k) {
+      uint64_t *qk = Qd + (size_t)k * nb, *uk = UEd + (size_t)2 * k * nb, *ek = uk + nb;
+      if (k == B - 1) {
+        PSC_CUDA(cudaMemcpyAsync(uk, qk, (size_t)nb * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+        PSC_CUDA(cudaMemsetAsync(ek, 0, (size_t)nb * 8, ctx->stream));
+        break;
+      }
+      const long m = blen(k), per = pcs.per[k], u_off = per * rank;
+      const long cnt = std::max(0L, std::min(per, m + 1 - u_off));
+      uint64_t e_base = 0;
+      for (int h = 0; h < rank; ++h) e_base += tot[(size_t)h * B + k];
+      merge_split_slice(ctx, pcs.gap[k].p, cnt, u_off, e_base, pcs.carry[k].p, cnt > 0 && u_off + cnt == m + 1, qk, nb, uk, ek);
+      cm.allreduce_sum_u64(ctx, uk, (size_t)2 * nb);
+      merge_split_next(ctx, qk, uk, nb, qk + nb);
+    }
+    std::vector<uint64_t> ue((size_t)2 * B * nb);
+    d2h(ctx, plan.q.data(), Qd, (size_t)B * nb);
+    d2h(ctx, ue.data(), UEd, ue.size());
+    sync(ctx);
+    for (long k = 0; k < B; ++k)
+      for (int i = 0; i < nb; ++i) {
+        plan.u[(size_t)k * nb + i] = ue[(size_t)2 * k * nb + i];
+        plan.e[(size_t)k * nb + i] = ue[(size_t)2 * k * nb + nb + i];
+      }
+  }
+  // exchange: my range needs entries [U(k, first[rank]), U(k, first[rank+1])) of every block's SA and gap array
+  auto need_lo = [&](long k, int g) { return (long)plan.U((int)k, first[g]); };
+  auto need_hi = [&](long k, int g) { return (long)plan.U((int)k, first[g + 1]); };
+  std::vector<size_t> sa_at(B + 1, 0), gap_at(B + 1, 0);  // offsets (entries) of block k's slices in the receive buffers
+  for (long k = 0; k < B; ++k) {
+    const size_t c = (size_t)(need_hi(k, rank) - need_lo(k, rank));
+    sa_at[k + 1] = sa_at[k] + ((c + 3) & ~(size_t)3);
+    gap_at[k + 1] = gap_at[k] + ((c + 1 + 3) & ~(size_t)3);
+  }
+  DevBuf<uint32_t> rsa(ctx, sa_at[B] + 4), rgap(ctx, gap_at[B] + 4);
+  {
+    KTrace kt(ctx, "merge_exchange");
+    cm.group_begin();
+    for (long k = 0; k < B; ++k) {
+      const int own = owner(k);
+      for (int g = 0; g < world; ++g) {  // block SA: from its owner
+        const long lo = need_lo(k, g), cnt = need_hi(k, g) - lo;
+        if (cnt <= 0) continue;
+        if (own == rank && g == rank)
+          PSC_CUDA(cudaMemcpyAsync(rsa.p + sa_at[k], pcs.sa[k].p + lo, (size_t)cnt * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        else if (own == rank) cm.send(ctx, pcs.sa[k].p + lo, (size_t)cnt * 4, g);
+        else if (g == rank) cm.recv(ctx, rsa.p + sa_at[k], (size_t)cnt * 4, own);
+      }
+      if (k == B - 1) continue;  // the rightmost block has no gap array
+      const long per = pcs.per[k], m = blen(k);
+      for (int h = 0; h < world; ++h) {      // holder of a slice of the gap counters
+        const long s0 = per * h, s1 = std::min(m + 1, s0 + per);
+        for (int g = 0; g < world; ++g) {    // receiver
+          if (h != rank && g != rank) continue;
+          const long lo = overlap_lo(s0, need_lo(k, g)), cnt = overlap_len(s0, s1, need_lo(k, g), need_hi(k, g));
+          if (cnt <= 0) continue;
+          uint32_t *dst = rgap.p + gap_at[k] + (lo - need_lo(k, rank));
+          if (h == rank && g == rank)
+            PSC_CUDA(cudaMemcpyAsync(dst, pcs.gap[k].p + (lo - s0), (size_t)cnt * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+          else if (h == rank) cm.send(ctx, pcs.gap[k].p + (lo - s0), (size_t)cnt * 4, g);
+          else cm.recv(ctx, dst, (size_t)cnt * 4, h);
         }
       }
     }
-    cur = nxt;
-    right_len += m;
-    std::swap(gt_cur, gt_new);
-    sync(ctx);
-    mine[id].reset();
+    cm.group_end();
   }
-  {
-    const long a = share_begin(rank, n, world), b = share_begin(rank + 1, n, world);
-    if (slice_beg) *slice_beg = a;
-    if (slice_len) *slice_len = b - a;
-    pack_sa5(ctx, Mlo[cur].p, Mhi[cur].p, b - a, gather ? out_sa5_d + 5 * a : out_sa5_d);
-    if (gather && world > 1) {
-      for (int h = 0; h < world; ++h) {
-        const long ha = share_begin(h, n, world), hb = share_begin(h + 1, n, world);
-        if (hb > ha) coll(ctx, fn, user, PSC_COLL_BCAST, out_sa5_d + 5 * ha, (size_t)(hb - ha) * 5, h);
-      }
+  // cascade, chunk by chunk of my range
+  MergeScratch scr;
+  scr.reserve(ctx, std::min(share_begin(1, n, world), C) + 16, need_hi_plane(n));
+  std::vector<LevelSlice> lv(B);
+  const long my_beg = share_begin(rank, n, world);
+  for (int i = first[rank]; i < first[rank + 1]; ++i) {
+    const long a = (long)plan.Q(0, i), b = (long)plan.Q(0, i + 1);
+    for (long k = 0; k < B; ++k) {
+      const size_t d = (size_t)(plan.U((int)k, i) - (uint64_t)need_lo(k, rank));
+      lv[k] = plan.slice((int)k, i, rsa.p + sa_at[k] + d, rgap.p + gap_at[k] + d, k * max_block);
     }
+    cascade_chunk(ctx, lv.data(), (int)B, b - a, scr, out_slice5_d + 5 * (a - my_beg));
+  }
+  sync(ctx);  // the receive buffers are released with this frame
+}
+
+void construct_sa_dist(psc_context *ctx, Comm &cm, const uint8_t *text_d, long n, long max_block,
+                       uint8_t *out_slice5_d, long *slice_beg, long *slice_len) {
+  memset(&ctx->stats, 0, sizeof(ctx->stats));
+  ctx->launches = 0;
+  cm.n_calls = 0;
+  cm.bytes = 0;
+  const long a = share_begin(cm.rank, n, cm.world), b = share_begin(cm.rank + 1, n, cm.world);
+  *slice_beg = a;
+  *slice_len = b - a;
+  if (n == 0) return;
+  PhaseTimer total(ctx, &ctx->stats.ms_total);
+  max_block = std::min(max_block, (1L << 31) - 4096);
+  const long B = div_up(n, max_block);
+  ctx->stats.n_blocks = B;
+  DistPieces pcs;
+  DevBuf<uint64_t> totals_d;
+  dist_blocks(ctx, cm, text_d, n, max_block, B, pcs, totals_d);
+  if (B == 1) {  // one block: its owner (rank 0) holds the SA, everybody gets a slice of it
+    if (cm.world > 1) {
+      DevBuf<uint32_t> part(ctx, std::max(1L, b - a));
+      cm.group_begin();
+      for (int g = 0; g < cm.world; ++g) {
+        const long ga = share_begin(g, n, cm.world), gb = share_begin(g + 1, n, cm.world);
+        if (gb <= ga) continue;
+        if (cm.rank == 0 && g == 0)
+          PSC_CUDA(cudaMemcpyAsync(part.p, pcs.sa[0].p, (size_t)(gb - ga) * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        else if (cm.rank == 0) cm.send(ctx, pcs.sa[0].p + ga, (size_t)(gb - ga) * 4, g);
+        else if (g == cm.rank) cm.recv(ctx, part.p, (size_t)(gb - ga) * 4, 0);
+      }
+      cm.group_end();
+      pack_sa5_from_sa(ctx, part.p, b - a, 0, out_slice5_d);  // values are text positions already (the block begins at 0)
+      sync(ctx);
+    } else {
+      pack_sa5_from_sa(ctx, pcs.sa[0].p, n, 0, out_slice5_d);
+    }
+  } else {
+    dist_merge(ctx, cm, n, max_block, B, pcs, totals_d, out_slice5_d);
   }
   sync(ctx);
   ctx->stats.kernel_launches = ctx->launches;
 }
 
-// ---- one GPU, two streams -------------------------------------------------------------------------
-// The same two phases overlapped on ONE device: a sorter thread with its own context (stream, buffer
-// cache) sorts blocks right to left and runs at most PIPE_DEPTH blocks ahead; the calling thread
-// streams each sorted block through rank build, LF walk and merge.  The walk is bound by the HBM's
-// random-access rate; the sort kernels of the next blocks fill the gaps around it (rank build,
-// partition, accumulate, merge, host round trips).  While a walk kernel and a radix pass do run side
-// by side (512 walkers per SM leave room for a sort CTA) they contend for the same HBM: the walk
-// slows from 98 to 129 ms and the passes from 41 to 106 ms, so the gain on 8 x 128 MiB is modest
-// (274 -> 264 ms); it costs the memory of the blocks sorted ahead, so api.cu only takes this path
-// when HBM allows.
-constexpr int PIPE_DEPTH = 2;
-
-struct SortQueue {
-  std::mutex mu;
-  std::condition_variable cv;
-  std::deque<std::unique_ptr<OwnedBlock>> ready;
-  long consumed = 0, produced = 0;
-  bool failed = false, cancel = false;
-  int fail_code = 0;
-  std::string fail_msg;
-};
-
-static psc_context *aux_context(psc_context *ctx) {
-  if (ctx->aux) return ctx->aux;
-  psc_context *a = new psc_context();
-  a->device = ctx->device;
-  a->n_sm = ctx->n_sm;
-  a->pool = ctx->pool;
-  a->trace = ctx->trace;
-  PSC_CUDA(cudaStreamCreateWithFlags(&a->stream, cudaStreamNonBlocking));
-  PSC_CUDA(cudaStreamCreateWithFlags(&a->side, cudaStreamNonBlocking));
-  memset(&a->stats, 0, sizeof(a->stats));
-  ctx->aux = a;
-  return a;
-}
-
-void construct_sa_pipelined(psc_context *ctx, const uint8_t *text_d, long n, long max_block, uint8_t *out_sa5_d) {
-  memset(&ctx->stats, 0, sizeof(ctx->stats));
-  ctx->launches = 0;
-  if (n == 0) return;
-  psc_context *aux = aux_context(ctx);
-  memset(&aux->stats, 0, sizeof(aux->stats));
-  aux->launches = 0;
-  PhaseTimer total(ctx, &ctx->stats.ms_total);
-  max_block = std::min(max_block, (1L << 31) - 4096);
-  const long B = div_up(n, max_block);
-  ctx->stats.n_blocks = B;
-  auto bounds = [&](long id, long *beg, long *end) { *beg = id * max_block; *end = std::min(n, *beg + max_block); };
-
-  SortQueue q;
-  std::thread sorter([&] {
-    try {
-      PSC_CUDA(cudaSetDevice(aux->device));
-      for (long id = B - 1; id >= 0; --id) {
-        {
-          std::unique_lock<std::mutex> lk(q.mu);
-          q.cv.wait(lk, [&] { return q.cancel || q.produced - q.consumed < PIPE_DEPTH; });
-          if (q.cancel) return;
-        }
-        long beg, end;
-        bounds(id, &beg, &end);
-        auto ob = sort_owned_block(aux, text_d, n, beg, end);
-        std::lock_guard<std::mutex> lk(q.mu);
-        q.ready.push_back(std::move(ob));
-        q.produced++;
-        q.cv.notify_all();
-      }
-    } catch (const CudaError &e) {
-      std::lock_guard<std::mutex> lk(q.mu);
-      q.failed = true;
-      q.fail_code = e.code;
-      q.fail_msg = psc_last_error();
-      q.cv.notify_all();
-    }
-  });
-  struct Joiner {  // the sorter must be gone before the queue or any buffer is
-    SortQueue &q; std::thread &t;
-    ~Joiner() { { std::lock_guard<std::mutex> lk(q.mu); q.cancel = true; q.cv.notify_all(); } if (t.joinable()) t.join(); }
-  } joiner{q, sorter};
-
-  const int walkers_before = ctx->walk_threads_per_sm;
-  if (const char *e = getenv("PSC_PIPE_WALK_TPS")) ctx->walk_threads_per_sm = atoi(e);
-  struct Restore { psc_context *c; int v; ~Restore() { c->walk_threads_per_sm = v; } } restore{ctx, walkers_before};
-
-  const long gwords = (n + 1 + 31) / 32 + 2;
-  DevBuf<uint32_t> Ga(ctx, gwords), Gb(ctx, gwords);
-  Ga.zero(); Gb.zero();
-  uint32_t *gt_cur = Ga.p, *gt_new = Gb.p;
-  DevBuf<uint32_t> Mlo[2];
-  DevBuf<uint8_t> Mhi[2];
-  for (int k = 0; k < 2; ++k) { Mlo[k].alloc(ctx, n); if (need_hi_plane(n)) Mhi[k].alloc(ctx, n);  /* high bytes only above 4 GiB */ }
-  int cur = 0;
-  long right_len = 0;
-  for (long id = B - 1; id >= 0; --id) {
-    long beg, end;
-    bounds(id, &beg, &end);
-    const long m = end - beg, t = n - end;
-    std::unique_ptr<OwnedBlock> ob;
-    {
-      std::unique_lock<std::mutex> lk(q.mu);
-      q.cv.wait(lk, [&] { return q.failed || !q.ready.empty(); });
-      if (q.failed) { set_error("%s", q.fail_msg.c_str()); throw CudaError{q.fail_code}; }
-      ob = std::move(q.ready.front());
-      q.ready.pop_front();
-    }
-    PSC_CUDA(cudaMemsetAsync(gt_new, 0, gwords * 4, ctx->stream));
-    DevBuf<uint32_t> gap;
-    if (t > 0) {
-      gap.alloc(ctx, m + 1);
-      gap.zero();
-      psc_rank *rk = rank_build(ctx, ob->bwt.p, m, ob->i0);
-      try {
-        uint64_t Cmap[256], run = 0;
-        for (int c = 0; c < 256; ++c) { Cmap[c] = run; run += (uint64_t)rk->counts[c] + (c == ob->last ? 1 : 0); }
-        walk_tail_range(ctx, rk, ob->i0, ob->last, Cmap, text_d + beg, ob->sa.p, m, text_d + end, t, 0, t, gt_cur, end,
-                        id > 0 ? gt_new : nullptr, gap.p);
-      } catch (...) { rank_free(rk); throw; }
-      rank_free(rk);
-    }
-    if (id > 0) {
-      if (m > 1) {
-        or_bits_shifted_kernel<<<(unsigned)div_up(div_up(m - 1, 32), 256), 256, 0, ctx->stream>>>(gt_new, beg, ob->gtb.p, m - 1);
-        PSC_LAUNCH_CHECK();
-      }
-      if (ob->end_bit) { set_bit_kernel<<<1, 1, 0, ctx->stream>>>(gt_new, end - 1); PSC_LAUNCH_CHECK(); }
-      ctx->launches += 2;
-    }
-    int nxt = 1 - cur;
-    merge_level(ctx, ob->sa.p, gap.p, m, beg, Mlo[cur].p, Mhi[cur].p, right_len, Mlo[nxt].p, Mhi[nxt].p);
-    cur = nxt;
-    right_len += m;
-    std::swap(gt_cur, gt_new);
-    sync(ctx);   // the block's buffers go back to the sorter's cache: nothing of ours may still read them
-    ob.reset();
-    {
-      std::lock_guard<std::mutex> lk(q.mu);
-      q.consumed++;
-      q.cv.notify_all();
-    }
-  }
-  pack_sa5(ctx, Mlo[cur].p, Mhi[cur].p, n, out_sa5_d);
-  sync(ctx);
-  // the sorter's counters belong to the same construction
-  const psc_stats &a = aux->stats;
-  ctx->stats.ms_gt_end += a.ms_gt_end; ctx->stats.ms_sort += a.ms_sort; ctx->stats.ms_radix += a.ms_radix;
-  ctx->stats.ms_bwt += a.ms_bwt; ctx->stats.ms_radix_pass += a.ms_radix_pass;
-  ctx->stats.radix_passes += a.radix_passes; ctx->stats.radix_elems += a.radix_elems; ctx->stats.radix_bytes += a.radix_bytes; ctx->stats.radix_keygen_bytes += a.radix_keygen_bytes; ctx->stats.ms_radix_keygen += a.ms_radix_keygen;
-  ctx->stats.doubling_rounds += a.doubling_rounds;
-  ctx->stats.kernel_launches = ctx->launches + aux->launches;
-  for (auto &r : aux->trace_rows) ctx->trace_rows.push_back(r);
-  aux->trace_rows.clear();
-}
-
 }  // namespace psc
 
-static int dist_entry(psc_context *ctx, const uint8_t *text_d, long n, long max_block, uint8_t *out_sa5_d, int rank,
-                      int world, psc_collective_fn fn, void *user, bool gather, long *slice_beg, long *slice_len,
-                      const char *who) {
+using namespace psc;
+
+extern "C" {
+
+int psc_dist_unique_id(uint8_t id[128]) {
+  if (!id) { set_error("psc_dist_unique_id: null pointer"); return PSC_EARG; }
+  return nccl_unique_id(id);
+}
+
+int psc_dist_init(psc_context *ctx, const uint8_t id[128], int rank, int world) {
+  if (!ctx || world < 1 || rank < 0 || rank >= world || (world > 1 && !id)) { set_error("psc_dist_init: bad argument"); return PSC_EARG; }
+  cudaSetDevice(ctx->device);
+  if (ctx->comm) { nccl_comm_destroy(ctx->comm); delete ctx->comm; ctx->comm = nullptr; }
+  Comm *c = new Comm();
+  int rc = nccl_comm_init(c, id, rank, world);
+  if (rc != PSC_OK) { delete c; return rc; }
+  ctx->comm = c;
+  return PSC_OK;
+}
+
+int psc_dist_finalize(psc_context *ctx) {
+  if (!ctx) return PSC_OK;
+  if (ctx->comm) {
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    nccl_comm_destroy(ctx->comm);
+    delete ctx->comm;
+    ctx->comm = nullptr;
+  }
+  return PSC_OK;
+}
+
+int psc_dist_stats(psc_context *ctx, long *n_collectives, double *bytes) {
+  if (!ctx || !ctx->comm) { set_error("psc_dist_stats: psc_dist_init has not been called"); return PSC_EARG; }
+  if (n_collectives) *n_collectives = ctx->comm->n_calls;
+  if (bytes) *bytes = ctx->comm->bytes;
+  return PSC_OK;
+}
+
+long psc_dist_slice_capacity(long n, int world) {
+  return world < 1 || n < 0 ? 0 : share_begin(1, n, world);
+}
+
+int psc_construct_sa_dist_slice_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
+                                  uint8_t *out_slice_sa5_d, long *slice_beg, long *slice_len) {
   try {
-    if (!ctx || n < 0 || (n > 0 && (!text_d || !out_sa5_d)) || world < 1 || rank < 0 || rank >= world ||
-        max_block <= 0 || (world > 1 && !fn)) {
-      psc::set_error("bad argument: %s", who);
+    if (!ctx || n < 0 || (n > 0 && (!text_d || !out_slice_sa5_d)) || max_block <= 0 || !slice_beg || !slice_len) {
+      set_error("bad argument: psc_construct_sa_dist_slice_d");
       return PSC_EARG;
     }
     PSC_CUDA(cudaSetDevice(ctx->device));
-    if (slice_beg) *slice_beg = 0;
-    if (slice_len) *slice_len = 0;
-    psc::construct_sa_dist(ctx, text_d, n, max_block, out_sa5_d, rank, world, fn, user, gather, slice_beg, slice_len);
-    psc::trace_report(ctx);
+    Comm self;  // a context without psc_dist_init is a world of one
+    construct_sa_dist(ctx, ctx->comm ? *ctx->comm : self, text_d, n, max_block, out_slice_sa5_d, slice_beg, slice_len);
+    trace_report(ctx);
     return PSC_OK;
-  } catch (const psc::CudaError &e) {
+  } catch (const CudaError &e) {
     return e.code;
   }
 }
 
-extern "C" int psc_construct_sa_dist_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
-                                       uint8_t *out_sa5_d, int rank, int world, psc_collective_fn fn,
-                                       void *user) {
-  return dist_entry(ctx, text_d, n, max_block, out_sa5_d, rank, world, fn, user, true, nullptr, nullptr,
-                    "psc_construct_sa_dist_d");
+int psc_construct_sa_dist_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block, uint8_t *out_sa5_d) {
+  try {
+    if (!ctx || n < 0 || (n > 0 && (!text_d || !out_sa5_d)) || max_block <= 0) {
+      set_error("bad argument: psc_construct_sa_dist_d");
+      return PSC_EARG;
+    }
+    PSC_CUDA(cudaSetDevice(ctx->device));
+    Comm self;
+    Comm &cm = ctx->comm ? *ctx->comm : self;
+    long a = 0, len = 0;
+    construct_sa_dist(ctx, cm, text_d, n, max_block, out_sa5_d + 5 * share_begin(cm.rank, n, cm.world), &a, &len);
+    // every rank receives the other slices
+    for (int h = 0; h < cm.world; ++h) {
+      const long ha = share_begin(h, n, cm.world), hb = share_begin(h + 1, n, cm.world);
+      if (hb > ha) cm.bcast(ctx, out_sa5_d + 5 * ha, (size_t)(hb - ha) * 5, h);
+    }
+    sync(ctx);
+    trace_report(ctx);
+    return PSC_OK;
+  } catch (const CudaError &e) {
+    return e.code;
+  }
 }
 
-extern "C" int psc_construct_sa_dist_slice_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
-                                             uint8_t *out_slice_sa5_d, long *slice_beg, long *slice_len, int rank,
-                                             int world, psc_collective_fn fn, void *user) {
-  if (!slice_beg || !slice_len) { psc::set_error("bad argument: psc_construct_sa_dist_slice_d"); return PSC_EARG; }
-  return dist_entry(ctx, text_d, n, max_block, out_slice_sa5_d, rank, world, fn, user, false, slice_beg, slice_len,
-                    "psc_construct_sa_dist_slice_d");
-}
-
-extern "C" long psc_dist_slice_capacity(long n, int world) {
-  return world < 1 || n < 0 ? 0 : psc::share_begin_public(1, n, world);
-}
+}  // extern "C"

@@ -287,13 +287,11 @@ void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, con
   ctx->stats.walkers = nwalk;
 }
 
-// Stages 2+3 for tail positions [lo, hi) of the text after a block: in chunks of at most
-// PSC_WALK_CHUNK positions (2^29: 4 GB of rank-stream scratch whatever the tail length), each chunk
-// cut into equal walker slices with boundaries on multiples of 32 (compute_gap.hpp:68-69 cuts the
-// tail over threads the same way), initial ranks by binary search, then the walk.
-void walk_tail_range(psc_context *ctx, const psc_rank *rk, long i0, uint8_t last, const uint64_t *Cmap,
-                     const uint8_t *block_d, const uint32_t *sa_d, long m, const uint8_t *after_d, long t,
-                     long lo, long hi, const uint32_t *gt_cur, long gt_off, uint32_t *gt_new, uint32_t *gap_d) {
+// Walkers for tail positions [lo, hi): chunks of at most PSC_WALK_CHUNK positions (2^29: 4 GB of rank-stream
+// scratch whatever the tail length), each chunk cut into equal walker slices with boundaries on multiples of
+// 32 from the chunk start (compute_gap.hpp:68-69 cuts the tail over threads the same way).  Walker k covers
+// [b[k], b[k+1]) and starts from the rank of suffix(after + b[k+1]).
+void make_walk_plan(psc_context *ctx, long lo, long hi, WalkPlan *p) {
   static long chunk = 0, target_env = -1;
   if (!chunk) {
     const char *e = getenv("PSC_WALK_CHUNK");
@@ -302,22 +300,47 @@ void walk_tail_range(psc_context *ctx, const psc_rank *rk, long i0, uint8_t last
     target_env = w ? std::max(1L, atol(w)) : 0;
   }
   const long target = target_env > 0 ? target_env : (long)ctx->n_sm * ctx->walk_threads_per_sm;
-  std::vector<uint64_t> wb;
+  p->b.clear();
+  p->chunk_at.clear();
   for (long clo = lo; clo < hi; clo += chunk) {
     const long chi = std::min(hi, clo + chunk);
-    long slice = std::max(64L, div_up(div_up(chi - clo, target), 32) * 32);
+    const long slice = std::max(64L, div_up(div_up(chi - clo, target), 32) * 32);
     const long W = div_up(chi - clo, slice);
-    wb.resize(W + 1);
-    for (long k = 0; k < W; ++k) wb[k] = (uint64_t)(clo + k * slice);
-    wb[W] = (uint64_t)chi;
-    DevBuf<uint64_t> wb_d(ctx, W + 1), sr_d(ctx, W);
-    h2d(ctx, wb_d.p, wb.data(), wb.size());
-    // walker k starts from the rank of suffix(after + wb[k+1]); the one ending at t from suffix(n): 0
-    initial_ranks(ctx, block_d, sa_d, m, after_d, t, 1, gt_cur, gt_off, W, wb_d.p + 1, sr_d.p);
-    lf_walk(ctx, rk, (uint32_t)i0, last, Cmap, after_d, chi - clo, clo, W, wb_d.p, sr_d.p, gt_cur, gt_off, gt_new,
-            gt_off, gap_d);
-    sync(ctx);  // wb is reused by the next chunk
+    p->chunk_at.push_back((long)p->b.size());
+    for (long k = 0; k < W; ++k) p->b.push_back((uint64_t)(clo + k * slice));
   }
+  p->chunk_at.push_back((long)p->b.size());
+  p->b.push_back((uint64_t)hi);
+}
+
+// K6 over a plan: b_d = the plan's boundaries on the device (W + 1), sr_d[k] = start rank of walker k
+void walk_with_plan(psc_context *ctx, const psc_rank *rk, long i0, uint8_t last, const uint64_t *Cmap,
+                    const uint8_t *after_d, const WalkPlan &p, const uint64_t *b_d, const uint64_t *sr_d,
+                    const uint32_t *gt_cur, long gt_off, uint32_t *gt_new, uint32_t *gap_d) {
+  for (size_t c = 0; c + 1 < p.chunk_at.size(); ++c) {
+    const long k0 = p.chunk_at[c], k1 = p.chunk_at[c + 1];
+    if (k1 <= k0) continue;
+    const long clo = (long)p.b[k0], chi = (long)p.b[k1];
+    lf_walk(ctx, rk, (uint32_t)i0, last, Cmap, after_d, chi - clo, clo, k1 - k0, b_d + k0, sr_d + k0, gt_cur, gt_off,
+            gt_new, gt_off, gap_d);
+  }
+}
+
+// Stages 2+3 for tail positions [lo, hi) of the text after a block: plan, initial ranks by binary search
+// over the block SA (K5), then the walk (K6).
+void walk_tail_range(psc_context *ctx, const psc_rank *rk, long i0, uint8_t last, const uint64_t *Cmap,
+                     const uint8_t *block_d, const uint32_t *sa_d, long m, const uint8_t *after_d, long t,
+                     long lo, long hi, const uint32_t *gt_cur, long gt_off, uint32_t *gt_new, uint32_t *gap_d) {
+  if (hi <= lo) return;
+  WalkPlan p;
+  make_walk_plan(ctx, lo, hi, &p);
+  const long W = (long)p.b.size() - 1;
+  DevBuf<uint64_t> b_d(ctx, W + 1), sr_d(ctx, W);
+  h2d(ctx, b_d.p, p.b.data(), p.b.size());
+  // walker k starts from the rank of suffix(after + b[k+1]); the one ending at t from suffix(n): 0
+  initial_ranks(ctx, block_d, sa_d, m, after_d, t, 1, gt_cur, gt_off, W, b_d.p + 1, sr_d.p);
+  walk_with_plan(ctx, rk, i0, last, Cmap, after_d, p, b_d.p, sr_d.p, gt_cur, gt_off, gt_new, gap_d);
+  sync(ctx);  // p.b is a host vector the async copy read
 }
 
 }  // namespace psc

@@ -1,22 +1,13 @@
-"""Multi-GPU driver: one process per GPU (torch.distributed), the block pipeline of
-csrc/dist.cu with its collectives served by NCCL (or gloo on CPU buffers in the host-logic tests).
-
-Sharding: block sorts on separate GPUs, the tail walk of every block split into
-`world` contiguous shares, per-GPU gap counts summed (all-reduce over NVLink), gt bits OR-ed, and the
-merge sharded by output range: every rank keeps n/world entries of the merged sequence and fetches the
-range of the previous level it needs with one all-to-all.
+"""Multi-GPU driver: one process per GPU (torchrun).  The schedule and every collective live in the
+library (csrc/dist.cu over NCCL, csrc/comm.cu); torch.distributed is only used to hand the NCCL id of
+rank 0 to the other ranks.  The plan helpers below restate, in plain Python, how csrc/dist.cu cuts the
+work (block owners, tail shares, gap slices, output shares, the split of an output boundary over the
+blocks); tests/test_dist_gloo.py runs them with world_size 2 on CPU.
 """
 import ctypes as C
 import numpy as np
 
-COLL_BCAST, COLL_ALLREDUCE_SUM_U32, COLL_ALLTOALLV = 1, 2, 3
-COLLECTIVE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_int)
-
-
-class AllToAllVArgs(C.Structure):
-    """psc_alltoallv_args (include/psascan_cuda.h): host struct the library passes for COLL_ALLTOALLV"""
-    _fields_ = [("send_d", C.c_void_p), ("recv_d", C.c_void_p),
-                ("send_bytes", C.POINTER(C.c_size_t)), ("recv_bytes", C.POINTER(C.c_size_t))]
+COARSE_TILE = 2048
 
 
 def share_begin(g, length, world):
@@ -36,87 +27,103 @@ def block_owner(block_id, n_blocks, world):
     return (n_blocks - 1 - block_id) % world
 
 
-def tail_share(t, rank, world):
-    """contiguous share [lo, hi) of a tail of t symbols, boundaries on multiples of 32"""
-    per = -(-(-(-t // world)) // 32) * 32
-    return min(t, per * rank), min(t, per * (rank + 1))
+def tail_shares(end, n, world):
+    """(first gt word touched, words per rank, world + 1 tail-relative boundaries): rank g walks tail
+    positions [lo[g], lo[g+1]) of the block ending at `end` and writes the gt bits [end + lo[g], end +
+    lo[g+1]), whole 32-bit words except at both ends (csrc/dist.cu tail_shares)"""
+    wl, wh = end >> 5, (n - 1) >> 5
+    per_w = -(-(wh - wl + 1) // world)
+    lo = [min(n, max(end, 32 * (wl + g * per_w))) - end for g in range(world + 1)]
+    return wl, per_w, lo
 
 
-class _CudaView:
-    def __init__(self, ptr, nbytes, typestr):
-        item = int(typestr[-1])
-        self.__cuda_array_interface__ = {"shape": (nbytes // item,), "typestr": typestr, "data": (ptr, False),
-                                         "version": 3, "strides": None}
+def gap_slice_len(m, world):
+    """entries of a block's gap array (m + 1 counters) every rank keeps after the reduce-scatter"""
+    return (-(-(m + 1) // world) + 3) // 4 * 4
 
 
-def tensor_from_pointer(ptr, nbytes, dtype_str, cuda):
-    """zero-copy torch view of a raw buffer: dtype_str 'u1' or 'i4'"""
-    import torch
-    if cuda:
-        return torch.as_tensor(_CudaView(ptr, nbytes, "|u1" if dtype_str == "u1" else "<i4"), device="cuda")
-    ctype = C.c_uint8 if dtype_str == "u1" else C.c_int32
-    item = 1 if dtype_str == "u1" else 4
-    arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ctype)), shape=(nbytes // item,))
-    return torch.from_numpy(arr)
+def split_in_slice(gap_slice, u_off, e_base, last_slice, q):
+    """merge_split_kernel (csrc/finalmerge.cu) for one query: the slice holds gap[u_off : u_off + cnt),
+    E[u_off] = e_base.  Returns (u, E[u]) for the largest u with u + E[u] <= q when that u lies in the
+    slice, else (0, 0): the answers of all slices of a block are summed."""
+    cnt = len(gap_slice)
+    if cnt == 0:
+        return 0, 0
+    total = int(np.sum(gap_slice, dtype=np.uint64))
+    if not (u_off + e_base <= q):
+        return 0, 0
+    if not last_slice and (u_off + cnt + e_base + total <= q):
+        return 0, 0
+    k, e = 0, e_base
+    while k < cnt - 1 and (u_off + k + 1) + e + int(gap_slice[k]) <= q:
+        e += int(gap_slice[k])
+        k += 1
+    return u_off + k, e
 
 
-def make_collective(cuda=True, group=None):
-    """the psc_collective_fn served by torch.distributed; returns (ctypes callback, call counter)"""
-    import torch
-    import torch.distributed as dist
-    counter = {"bcast": 0, "allreduce": 0, "alltoall": 0, "bytes": 0}
-    world = dist.get_world_size(group) if dist.is_initialized() else 1
-
-    def fn(user, op, buf, nbytes, root):
-        try:
-            if op == COLL_BCAST:
-                t = tensor_from_pointer(buf, nbytes, "u1", cuda)
-                dist.broadcast(t, src=root, group=group)
-                counter["bcast"] += 1
-            elif op == COLL_ALLREDUCE_SUM_U32:
-                # uint32 counters summed as int32: two's-complement addition is the same
-                t = tensor_from_pointer(buf, nbytes, "i4", cuda)
-                dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
-                counter["allreduce"] += 1
-            elif op == COLL_ALLTOALLV:
-                a = C.cast(buf, C.POINTER(AllToAllVArgs)).contents
-                sb = [int(a.send_bytes[h]) for h in range(world)]
-                rb = [int(a.recv_bytes[h]) for h in range(world)]
-                empty = torch.empty(0, dtype=torch.uint8, device="cuda" if cuda else "cpu")
-                src = tensor_from_pointer(a.send_d, sum(sb), "u1", cuda) if sum(sb) else empty
-                dst = tensor_from_pointer(a.recv_d, sum(rb), "u1", cuda) if sum(rb) else empty
-                dist.all_to_all_single(dst, src, output_split_sizes=rb, input_split_sizes=sb, group=group)
-                counter["alltoall"] += 1
-            else:
-                return 1
-            counter["bytes"] += nbytes
-            if cuda:
-                torch.cuda.current_stream().synchronize()
-            return 0
-        except Exception as e:  # never let an exception cross the C boundary
-            print("psascan_b200.dist collective failed:", repr(e), flush=True)
-            return 2
-
-    return COLLECTIVE_FN(fn), counter
+def merge_boundaries(n, world, chunk):
+    """(all chunk boundaries in order, index of every rank's first one): rank g's output range cut into
+    chunks (csrc/dist.cu dist_merge)"""
+    bd, first = [], []
+    for g in range(world):
+        first.append(len(bd))
+        bd.extend(range(share_begin(g, n, world), share_begin(g + 1, n, world), chunk))
+    first.append(len(bd))
+    bd.append(n)
+    return bd, first
 
 
-def _rank_world(rank, world):
+def cascade_chunk(levels):
+    """finalmerge.cu cascade_chunk in numpy: levels = [(sa_slice + beg as int64, gap_slice, skip)] left to
+    right; returns the merged chunk"""
+    merged = np.zeros(0, dtype=np.int64)
+    for sa, gap, skip in reversed(levels):
+        cb = len(sa)
+        if cb == 0:
+            continue
+        if len(merged) == 0:
+            merged = sa.copy()
+            continue
+        g = np.asarray(gap[:cb], dtype=np.int64).copy()
+        g[0] -= skip
+        slot = np.arange(cb, dtype=np.int64) + np.cumsum(g)
+        out = np.zeros(cb + len(merged), dtype=np.int64)
+        mask = np.zeros(len(out), dtype=bool)
+        mask[slot] = True
+        out[mask] = sa
+        out[~mask] = merged
+        merged = out
+    return merged
+
+
+# ---- the library over NCCL -------------------------------------------------------------------------------
+def init(ctx, rank=None, world=None):
+    """collective: joins `ctx` to an NCCL communicator of all torch.distributed ranks (psc_dist_init)"""
     import torch.distributed as dist
     if world is None:
         world = dist.get_world_size() if dist.is_initialized() else 1
         rank = dist.get_rank() if dist.is_initialized() else 0
+    ident = (C.c_uint8 * 128)()
+    if world > 1:
+        box = [None]
+        if rank == 0:
+            ctx._chk(ctx.lib.psc_dist_unique_id(ident))
+            box[0] = bytes(ident)
+        dist.broadcast_object_list(box, src=0)
+        ident = (C.c_uint8 * 128).from_buffer_copy(box[0])
+    ctx._chk(ctx.lib.psc_dist_init(ctx.h, ident, C.c_int(rank), C.c_int(world)))
+    ctx.dist_rank, ctx.dist_world = rank, world
     return rank, world
 
 
-def construct_sa_distributed(ctx, text_dev_ptr, n, out_dev_ptr, max_block, rank=None, world=None):
-    """SPMD call: every rank passes the whole text (device pointer) and gets the whole SA."""
-    rank, world = _rank_world(rank, world)
-    cb, counter = make_collective(cuda=True)
-    f = ctx.lib.psc_construct_sa_dist_d
-    rc = f(ctx.h, C.c_void_p(text_dev_ptr), C.c_long(n), C.c_long(max_block), C.c_void_p(out_dev_ptr),
-           C.c_int(rank), C.c_int(world), cb, None)
-    ctx._chk(rc)
-    return counter
+def finalize(ctx):
+    ctx.lib.psc_dist_finalize(ctx.h)
+
+
+def comm_stats(ctx):
+    calls, nbytes = C.c_long(0), C.c_double(0)
+    ctx._chk(ctx.lib.psc_dist_stats(ctx.h, C.byref(calls), C.byref(nbytes)))
+    return {"collectives": calls.value, "bytes": nbytes.value}
 
 
 def slice_capacity(ctx, n, world):
@@ -125,14 +132,19 @@ def slice_capacity(ctx, n, world):
     return int(ctx.lib.psc_dist_slice_capacity(C.c_long(n), C.c_int(world)))
 
 
-def construct_sa_slices(ctx, text_dev_ptr, n, out_slice_dev_ptr, max_block, rank=None, world=None):
-    """SPMD call: every rank passes the whole text and keeps its slice of the SA (5-byte entries
+def construct_sa_slices(ctx, text_dev_ptr, n, out_slice_dev_ptr, max_block):
+    """SPMD call after init(): every rank passes the whole text and keeps its slice of the SA (5-byte entries
     [beg, beg + length) in out_slice_dev_ptr); returns (beg, length, collective counters)."""
-    rank, world = _rank_world(rank, world)
-    cb, counter = make_collective(cuda=True)
     beg, length = C.c_long(0), C.c_long(0)
     rc = ctx.lib.psc_construct_sa_dist_slice_d(ctx.h, C.c_void_p(text_dev_ptr), C.c_long(n), C.c_long(max_block),
-                                               C.c_void_p(out_slice_dev_ptr), C.byref(beg), C.byref(length),
-                                               C.c_int(rank), C.c_int(world), cb, None)
+                                               C.c_void_p(out_slice_dev_ptr), C.byref(beg), C.byref(length))
     ctx._chk(rc)
-    return beg.value, length.value, counter
+    return beg.value, length.value, (comm_stats(ctx) if getattr(ctx, "dist_world", 1) > 1 else {})
+
+
+def construct_sa_distributed(ctx, text_dev_ptr, n, out_dev_ptr, max_block):
+    """SPMD call after init(): every rank passes the whole text (device pointer) and gets the whole SA."""
+    rc = ctx.lib.psc_construct_sa_dist_d(ctx.h, C.c_void_p(text_dev_ptr), C.c_long(n), C.c_long(max_block),
+                                         C.c_void_p(out_dev_ptr))
+    ctx._chk(rc)
+    return comm_stats(ctx) if getattr(ctx, "dist_world", 1) > 1 else {}

@@ -14,7 +14,8 @@ EXPORTS = [
     "psc_bench_random_sectors", "psc_bench_radix_pass", "psc_device_alloc", "psc_device_free",
     "psc_pinned_alloc", "psc_pinned_free", "psc_copy_h2d", "psc_copy_d2h", "psc_device_info", "psc_construct_sa_dist_d",
     "psc_construct_sa_dist_slice_d", "psc_dist_slice_capacity", "psc_verify_sa_d",
-    "psc_verify_sa_noalloc_d", "psc_verify_noalloc_max_n",
+    "psc_verify_sa_noalloc_d", "psc_verify_noalloc_max_n", "psc_dist_unique_id", "psc_dist_init",
+    "psc_dist_finalize", "psc_dist_stats",
 ]
 
 
@@ -223,10 +224,10 @@ class Context:
         f = self.lib.psc_construct_sa_d if device else self.lib.psc_construct_sa
         self._chk(f(self.h, C.c_void_p(text_ptr), C.c_long(n), C.c_long(max_block), C.c_void_p(out_ptr)))
 
-    def construct_sa_dist_ptr(self, text_dev_ptr, n, out_dev_ptr, max_block, rank=0, world=1, callback=None):
-        """csrc/dist.cu schedule; world == 1 needs no callback"""
+    def construct_sa_dist_ptr(self, text_dev_ptr, n, out_dev_ptr, max_block):
+        """csrc/dist.cu schedule; a context that never joined a communicator (psascan_b200.dist.init) is a world of one"""
         self._chk(self.lib.psc_construct_sa_dist_d(self.h, C.c_void_p(text_dev_ptr), C.c_long(n), C.c_long(max_block),
-                                                   C.c_void_p(out_dev_ptr), C.c_int(rank), C.c_int(world), callback, None))
+                                                   C.c_void_p(out_dev_ptr)))
 
     def verify_sa_ptr(self, text_dev_ptr, n, sa5_dev_ptr):
         """O(n) device check (psc_verify_sa_d): returns the four violation counts, all zero for a correct SA"""

@@ -18,6 +18,7 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 ctx = P.Context(local)
+D.init(ctx)
 ok = True
 cases = [(name, golden_text(gen, kw, n), sa5, [1000, n // 3 + 7]) for name, gen, kw, n, sa5 in golden_cases()]
 big = textgen.markov(1 << 24, seed=3)
@@ -61,6 +62,7 @@ for name, text, sa5, mbs in cases[-3:]:
     ok = ok and bool(flag.item())
     if rank == 0:
         print(f"slices {name} n={n} max_block={mbs[0]} world={world} ok={bool(flag.item())} shares {lens} coll {cnt}", flush=True)
+D.finalize(ctx)
 ctx.close()
 dist.destroy_process_group()
 sys.exit(0 if ok else 1)
