@@ -370,3 +370,67 @@ def test_verify_sa_device(ctx):
     k = next(i for i in range(n - 1) if text[sa[i]] != text[sa[i + 1]])
     bad = sa.copy(); bad[k], bad[k + 1] = bad[k + 1], bad[k]
     v = check(O.encode_uint40(bad)); assert v[:2] == [0, 0] and v[2] == 1
+
+
+def test_multi_gpu_dist_check_torchrun():
+    """csrc/dist.cu over NCCL on every visible GPU (at least 2): tools/dist_check.py compares both distributed
+    entry points with the golden .sa5 files and the single-GPU pipeline, bit for bit, and exits non-zero on
+    any difference."""
+    import os, subprocess, sys, torch
+    ngpu = torch.cuda.device_count()
+    if ngpu < 2:
+        pytest.skip("needs at least 2 GPUs (one rank per GPU)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    world = min(ngpu, 8)
+    port = 29600 + os.getpid() % 300
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(root, "tools", "dist_check.py")],
+                       capture_output=True, text=True, timeout=1200)
+    assert r.returncode == 0, (r.stdout[-3000:], r.stderr[-3000:])
+    assert "ok=False" not in r.stdout and r.stdout.count("ok=True") >= 10
+
+
+def test_config1_full_size_cmp_with_reference(tmp_path_factory):
+    """BASELINE configs[0] at its stated size: 200 MB of DNA-like text, host/construct_sa (GPU) against the
+    unmodified reference oracle/_ref/construct_sa -m 3584mi (the "3.5gi" of BASELINE.json: the option takes whole numbers only) -- the two .sa5 files (10^9 bytes) must be equal."""
+    import filecmp, os, shutil, subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ours, ref = os.path.join(root, "host", "construct_sa"), O.REF_BIN
+    if not (os.path.exists(ours) and os.path.exists(ref)):
+        pytest.skip("host/construct_sa or oracle/_ref/construct_sa not built")
+    base = "/dev/shm" if os.path.isdir("/dev/shm") and shutil.disk_usage("/dev/shm").free > (3 << 30) else None
+    d = tmp_path_factory.mktemp("cfg1") if base is None else None
+    work = str(d) if d is not None else os.path.join(base, "psc_cfg1_%d" % os.getpid())
+    os.makedirs(work, exist_ok=True)
+    try:
+        f = os.path.join(work, "dna200m.txt")
+        textgen.dna(200_000_000, seed=1).tofile(f)
+        threads = str(min(16, len(os.sched_getaffinity(0))))
+        subprocess.run([ref, f, "-o", f + ".ref.sa5", "-m", "3584mi"], check=True, stdin=subprocess.DEVNULL,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, env=dict(os.environ, OMP_NUM_THREADS=threads),
+                       timeout=1500)
+        subprocess.run([ours, f, "-o", f + ".gpu.sa5", "-m", "3584mi"], check=True, stdin=subprocess.DEVNULL,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=600)
+        assert os.path.getsize(f + ".gpu.sa5") == 1_000_000_000
+        assert filecmp.cmp(f + ".ref.sa5", f + ".gpu.sa5", shallow=False)
+    finally:
+        shutil.rmtree(work, ignore_errors=True)
+
+
+def test_config2_full_size_verified(ctx):
+    """BASELINE configs[1] at its stated size: 2^30 uniform random bytes (0..254), one block; the result goes
+    through the O(n) device check (no CPU sorter reaches this size inside a test)."""
+    import torch
+    n = 1 << 30
+    g = torch.Generator(device="cuda"); g.manual_seed(2)
+    text = torch.randint(0, 255, (n,), dtype=torch.uint8, device="cuda", generator=g)
+    out = torch.empty(5 * n, dtype=torch.uint8, device="cuda")
+    ctx.construct_sa_ptr(text.data_ptr(), n, out.data_ptr(), 0, device=True)
+    assert ctx.stats()["n_blocks"] == 1
+    assert ctx.verify_sa_ptr(text.data_ptr(), n, out.data_ptr()) == [0, 0, 0, 0]
+    # and the same text in 5 ragged blocks: rank planes of 255 symbols, gap arrays, the merge by output range
+    ctx.construct_sa_ptr(text.data_ptr(), 1 << 28, out.data_ptr(), (1 << 26) - 12345, device=True)
+    assert ctx.stats()["n_blocks"] == 5
+    assert ctx.verify_sa_ptr(text.data_ptr(), 1 << 28, out.data_ptr()) == [0, 0, 0, 0]
+    del text, out
+    torch.cuda.empty_cache()
