@@ -8,7 +8,9 @@
  *     the last error on the calling thread is psc_last_error().  (The reference prints and
  *     exits, e.g. src/utils.cpp:60-63; the host wrapper host/psascan.hpp does that.)
  *   - pointers are HOST pointers unless the name ends in _d (device pointers on the GPU the
- *     context was created on).
+ *     context was created on).  The library works on its own non-blocking CUDA streams and
+ *     returns after its work is complete: device inputs must be COMPLETE when a call is made
+ *     (synchronise the stream that produced them first), device outputs are ready on return.
  *   - gt bit vectors cross this boundary in the reference's layout: reversed, LSB-first
  *     (include/bitvector.hpp:61-67): for a vector covering text positions (lo, hi], bit r
  *     of byte r>>3 (mask 1 << (r & 7)) belongs to position hi - r, r in [0, hi-lo).

@@ -3,6 +3,7 @@
 #include <algorithm>
 #include "common.cuh"
 #include "finalmerge.cuh"
+#include "texthash.cuh"
 
 namespace psc {
 
@@ -75,7 +76,7 @@ WorkBudget *work_budget_arm(psc_context *ctx) {
   return wb;
 }
 
-void work_budget_check(psc_context *ctx, WorkBudget *wb, const char *what) {
+int work_budget_check(psc_context *ctx, WorkBudget *wb, const char *what) {
   WorkBudget h;
   cudaError_t e = cudaMemcpyAsync(&h, wb, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
@@ -86,6 +87,7 @@ void work_budget_check(psc_context *ctx, WorkBudget *wb, const char *what) {
               "(degenerate repeats across a block boundary); use one block or a larger max_block", what, h.limit);
     throw CudaError{PSC_ELIMIT};
   }
+  return h.need_hash;
 }
 
 // ---- buffer cache ------------------------------------------------------------------------------
@@ -267,6 +269,8 @@ static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, lon
   PhaseTimer total(ctx, &ctx->stats.ms_total);
   arg_check(max_block > 0, "text does not fit the HBM budget");
   max_block = std::min(max_block, (1L << 31) - 4096);
+  hash_domain_set(ctx, text_d, n);  // fingerprints for K0 / K5, built only if a comparison outlasts the cap
+  struct DomainGuard { psc_context *c; ~DomainGuard() { hash_domain_clear(c); } } domain_guard{ctx};
   long B = div_up(n, max_block);
   ctx->stats.n_blocks = B;
   long gwords = (n + 1 + 31) / 32 + 2;
@@ -384,6 +388,7 @@ int psc_init(int device, size_t hbm_budget, psc_context **out) {
 int psc_shutdown(psc_context *ctx) {
   if (!ctx) return PSC_OK;
   cudaSetDevice(ctx->device);
+  hash_domain_clear(ctx);
   cache_trim(ctx);
   cudaStreamSynchronize(ctx->stream);
   cudaMemPoolTrimTo(ctx->pool, 0);

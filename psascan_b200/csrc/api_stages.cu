@@ -2,6 +2,7 @@
 // reference seam (see include/psascan_cuda.h) and is what the parity tests call.
 #include <algorithm>
 #include "common.cuh"
+#include "texthash.cuh"
 
 namespace psc {
 template <typename F>
@@ -47,6 +48,9 @@ int psc_sort_block(psc_context *ctx, const uint8_t *text, long m, const uint8_t 
     need(m <= (1L << 31) - 4096, "psc_sort_block: block too long");
     PSC_CUDA(cudaSetDevice(ctx->device));
     long t = tail_prefix_len;
+    // fingerprints (K0) live on this call's own buffer: no domain may survive the call
+    hash_domain_clear(ctx);
+    struct DomainGuard { psc_context *c; ~DomainGuard() { hash_domain_clear(c); } } domain_guard{ctx};
     DevBuf<uint8_t> buf(ctx, m + t);  // block followed by the tail prefix, as in the text
     h2d(ctx, buf.p, text, m);
     if (t) h2d(ctx, buf.p + m, tail_prefix, t);
@@ -132,6 +136,8 @@ int psc_initial_ranks(psc_context *ctx, const uint8_t *block_text, const uint32_
     if (nstarts == 0) return;
     need(starts && out, "psc_initial_ranks: starts/out");
     PSC_CUDA(cudaSetDevice(ctx->device));
+    hash_domain_clear(ctx);
+    struct DomainGuard { psc_context *c; ~DomainGuard() { hash_domain_clear(c); } } domain_guard{ctx};
     DevBuf<uint8_t> buf(ctx, m + after_len);
     h2d(ctx, buf.p, block_text, m);
     if (after_len) h2d(ctx, buf.p + m, after_text, after_len);

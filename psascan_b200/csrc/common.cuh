@@ -35,10 +35,11 @@ static inline bool need_hi_plane(long n) { return n > (1L << 32) || getenv("PSC_
 
 }  // namespace psc
 
-namespace psc { struct Comm; }
+namespace psc { struct Comm; struct TextHashStore; }
 
 struct psc_context {
   int device = 0;
+  psc::TextHashStore *thash = nullptr;  // texthash.cu: fingerprints of the text of the running construction
   psc::Comm *comm = nullptr;  // psc_dist_init (comm.cu): this context is one rank of a multi-GPU construction
   int n_sm = 148;
   size_t hbm_budget = 0;
@@ -147,7 +148,7 @@ void trace_report(psc_context *ctx);
 // device-side work guard (see WorkBudget below): allocate + arm, and check after the kernel
 struct WorkBudget;
 WorkBudget *work_budget_arm(psc_context *ctx);
-void work_budget_check(psc_context *ctx, WorkBudget *wb, const char *what);
+int work_budget_check(psc_context *ctx, WorkBudget *wb, const char *what);  // returns the need_hash flag
 
 template <typename T>
 static inline void h2d(psc_context *ctx, T *dst, const T *src, size_t n) {
@@ -172,7 +173,7 @@ __device__ __forceinline__ void st_relaxed_u64(uint64_t *p, uint64_t v) {
 __device__ __forceinline__ bool bit_get(const uint32_t *bits, long i) {
   return (bits[i >> 5] >> (i & 31)) & 1u;
 }
-// 4 bytes from any address (little endian); may touch up to 7 bytes past p (buffers have slack)
+// 4 bytes from any address (little endian): reads the aligned word(s) that hold p[0..3]
 __device__ __forceinline__ uint32_t load_u32_any(const uint8_t *p) {
   uintptr_t a = (uintptr_t)p;
   const uint32_t *w = (const uint32_t *)(a & ~(uintptr_t)3);
@@ -196,33 +197,34 @@ __device__ __forceinline__ void store_bits_word(uint32_t *bits, long bitpos, uin
 // every text but degenerate ones (period far below the block length).  Every 4 KiB of matched
 // symbols are charged to a device counter; past the limit the kernels bail out and the host reports
 // PSC_ELIMIT instead of hanging the GPU for hours.
-struct WorkBudget { unsigned long long used, limit; int exceeded; int pad; };
+struct WorkBudget { unsigned long long used, limit; int exceeded; int need_hash; };
+
+// length of the common prefix of a[0..lim) and b[0..lim).  Whole words are only loaded while four symbols
+// remain, the rest goes byte by byte: nothing past a + lim or b + lim is ever read beyond the aligned word
+// that holds the last compared byte (callers pass texts of exactly n bytes).
+__device__ __forceinline__ long common_prefix(const uint8_t *a, const uint8_t *b, long lim) {
+  long el = 0;
+  while (el + 4 <= lim) {
+    uint32_t x = load_u32_any(a + el) ^ load_u32_any(b + el);
+    if (x) return el + ((__ffs(x) - 1) >> 3);
+    el += 4;
+  }
+  while (el < lim && a[el] == b[el]) ++el;
+  return el;
+}
 
 __device__ __forceinline__ long common_prefix_guarded(const uint8_t *a, const uint8_t *b, long lim, WorkBudget *wb) {
   long el = 0;
   while (el < lim) {
     const long stop = min(lim, el + 4096);
-    while (el < stop) {
-      uint32_t x = load_u32_any(a + el) ^ load_u32_any(b + el);
-      if (x) { el += (__ffs(x) - 1) >> 3; return el > lim ? lim : el; }
-      el += 4;
-    }
+    const long got = common_prefix(a + el, b + el, stop - el);
+    el += got;
+    if (el < stop) return el;
     if (el < lim) {
       if (atomicAdd(&wb->used, 4096ull) > wb->limit || *(volatile int *)&wb->exceeded) { wb->exceeded = 1; return -1; }
     }
   }
-  return el > lim ? lim : el;
-}
-
-// length of the common prefix of a[0..lim) and b[0..lim)
-__device__ __forceinline__ long common_prefix(const uint8_t *a, const uint8_t *b, long lim) {
-  long el = 0;
-  while (el < lim) {
-    uint32_t x = load_u32_any(a + el) ^ load_u32_any(b + el);
-    if (x) { el += (__ffs(x) - 1) >> 3; break; }
-    el += 4;
-  }
-  return el > lim ? lim : el;
+  return el;
 }
 #endif
 

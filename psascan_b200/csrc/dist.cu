@@ -23,6 +23,7 @@
 #include <string>
 #include "comm.cuh"
 #include "finalmerge.cuh"
+#include "texthash.cuh"
 
 namespace psc {
 
@@ -367,6 +368,8 @@ void construct_sa_dist(psc_context *ctx, Comm &cm, const uint8_t *text_d, long n
   if (n == 0) return;
   PhaseTimer total(ctx, &ctx->stats.ms_total);
   max_block = std::min(max_block, (1L << 31) - 4096);
+  hash_domain_set(ctx, text_d, n);  // K0 compares past the block end here: fingerprints bound it (texthash.cuh)
+  struct DomainGuard { psc_context *c; ~DomainGuard() { hash_domain_clear(c); } } domain_guard{ctx};
   const long B = div_up(n, max_block);
   ctx->stats.n_blocks = B;
   DistPieces pcs;

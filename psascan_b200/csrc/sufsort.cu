@@ -13,6 +13,7 @@
 #include <algorithm>
 #include <cmath>
 #include "scan.cuh"
+#include "texthash.cuh"
 
 namespace psc {
 
@@ -661,26 +662,71 @@ void sort_block(psc_context *ctx, const uint8_t *text_d, long m, const uint32_t 
 }
 
 // ---- K0: gt_end by matching the block against the text after it -------------------------------
-// compute_initial_gt_bitvectors.hpp:61-148 (semantics; brute force with 4-byte compares, the
-// reference's ms-decomposition speed-up is not reproduced).
-__global__ void __launch_bounds__(256)
-    gt_end_kernel(const uint8_t *__restrict__ block, long m, const uint8_t *__restrict__ after,
-                  long after_len, int after_is_text_end, const uint32_t *__restrict__ gt_after,
-                  long gt_after_off, uint32_t *__restrict__ out_bits, WorkBudget *wb) {
+// compute_initial_gt_bitvectors.hpp:61-148 (semantics).  Every position compares at most `cap` symbols
+// directly; a match that outlasts them is measured by fingerprints (texthash.cuh) in O(log) steps, so
+// the kernel is O(m * cap) in the worst case where the reference's ms-decomposition is O(m).
+//   cap <= 0: no fingerprints possible (block and tail not contiguous in one buffer): symbol by symbol
+//             under the work guard, as in round 1.
+struct GtEndArgs {
+  const uint8_t *block; long m;
+  const uint8_t *after; long after_len; int after_is_text_end;
+  const uint32_t *gt_after; long gt_after_off;
+  long off_block, off_after, cap;
+};
+
+__device__ __forceinline__ bool gt_end_general(const GtEndArgs &a, const HashView &hv, WorkBudget *wb, long p) {
   // gt_after == nullptr: the match simply continues past the block end into `after` (the block and
   // the text after it are contiguous), so no gt bits of the next block are needed.
-  long p = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  bool g = false;
-  if (p < m) {
-    long lim = gt_after ? min(m - p, after_len) : after_len;
-    long el = common_prefix_guarded(block + p, after, lim, wb);
-    if (el < 0) g = false;  // work guard tripped: the host discards the result
-    else if (el == after_len && after_is_text_end) g = true;
-    else if (gt_after && p + el == m) g = !bit_get(gt_after, gt_after_off + el - 1);
-    else g = block[p + el] > after[el];
+  const long lim = a.gt_after ? min(a.m - p, a.after_len) : a.after_len;
+  long el;
+  if (a.cap <= 0) {
+    el = common_prefix_guarded(a.block + p, a.after, lim, wb);
+  } else {
+    el = common_prefix(a.block + p, a.after, min(lim, a.cap));
+    if (el == a.cap && a.cap < lim) {
+      if (hv.pre) el = th_lcp(hv, a.off_block + p, a.off_after, a.cap, lim);
+      else { wb->need_hash = 1; el = -1; }  // the host builds the fingerprints and runs the kernel again
+    }
   }
-  uint32_t word = __ballot_sync(0xffffffffu, g);
-  if ((threadIdx.x & 31) == 0 && (p < m)) out_bits[p >> 5] = word;
+  if (el < 0) return false;  // result discarded by the host
+  if (el == a.after_len && a.after_is_text_end) return true;
+  if (a.gt_after && p + el == a.m) return !bit_get(a.gt_after, a.gt_after_off + el - 1);
+  return a.block[p + el] > a.after[el];
+}
+
+// One thread decides 8 consecutive positions (one byte of the bit array).  Almost every position differs from
+// the tail within its first four symbols: those are decided from a 12-byte register window against the first
+// word of the tail, without touching memory again; the rest go through gt_end_general.
+__global__ void __launch_bounds__(256)
+    gt_end_kernel(const __grid_constant__ GtEndArgs a, uint32_t *__restrict__ out_bits, WorkBudget *wb,
+                  const __grid_constant__ HashView hv) {
+  const long p8 = ((long)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (p8 >= a.m) return;
+  const bool fast = (p8 + 12 <= a.m) && a.after_len >= 4;
+  uint32_t w0 = 0, w1 = 0, w2 = 0, a4 = 0;
+  if (fast) {
+    w0 = load_u32_any(a.block + p8); w1 = load_u32_any(a.block + p8 + 4); w2 = load_u32_any(a.block + p8 + 8);
+    a4 = load_u32_any(a.after);
+  }
+  uint32_t bits = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const long p = p8 + i;
+    if (p >= a.m) break;
+    bool g, done = false;
+    if (fast) {
+      const uint32_t w = i < 4 ? __funnelshift_r(w0, w1, 8 * i) : __funnelshift_r(w1, w2, 8 * (i - 4));
+      const uint32_t x = w ^ a4;
+      if (x) {
+        const int sh = (__ffs(x) - 1) & ~7;
+        g = ((w >> sh) & 255u) > ((a4 >> sh) & 255u);
+        done = true;
+      }
+    }
+    if (!done) g = gt_end_general(a, hv, wb, p);
+    bits |= (g ? 1u : 0u) << i;
+  }
+  reinterpret_cast<uint8_t *>(out_bits)[p8 >> 3] = (uint8_t)bits;
 }
 
 void compute_gt_end(psc_context *ctx, const uint8_t *block_d, long m, const uint8_t *after_d,
@@ -688,12 +734,25 @@ void compute_gt_end(psc_context *ctx, const uint8_t *block_d, long m, const uint
                     long gt_after_off, uint32_t *gt_end_bits_d) {
   PhaseTimer timer(ctx, &ctx->stats.ms_gt_end);
   if (m == 0) return;
-  WorkBudget *wb = work_budget_arm(ctx);
-  gt_end_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(
-      block_d, m, after_d, after_len, after_is_text_end, gt_after_bits_d, gt_after_off, gt_end_bits_d, wb);
-  PSC_LAUNCH_CHECK();
-  ctx->launches++;
-  work_budget_check(ctx, wb, "gt_end (K0)");
+  const bool contiguous = (after_d == block_d + m) && after_len > 0;
+  long cap = (contiguous && hash_domain_ensure(ctx, block_d, after_d + after_len)) ? lcp_cap() : 0;
+  HashView hv;  // empty until the tables exist
+  if (cap > 0) hash_view(ctx, block_d, after_d + after_len, false, &hv);
+  for (int attempt = 0;; ++attempt) {
+    WorkBudget *wb = work_budget_arm(ctx);
+    GtEndArgs ga{block_d, m, after_d, after_len, after_is_text_end, gt_after_bits_d, gt_after_off,
+                 hv.pre ? (long)(block_d - hv.text) : 0, hv.pre ? (long)(after_d - hv.text) : 0, cap};
+    { KTrace kt(ctx, "gt_end");
+      gt_end_kernel<<<(unsigned)div_up(div_up(m, 8), 256), 256, 0, ctx->stream>>>(ga, gt_end_bits_d, wb, hv); }
+    PSC_LAUNCH_CHECK();
+    ctx->launches++;
+    if (!work_budget_check(ctx, wb, "gt_end (K0)")) return;
+    // some match outlasted the cap: build the fingerprints (once per construction) and decide everything again
+    if (attempt > 0 || !hash_view(ctx, block_d, after_d + after_len, true, &hv)) {
+      set_error("gt_end (K0): fingerprints unavailable");
+      throw CudaError{PSC_ECUDA};
+    }
+  }
 }
 
 // ---- K3: BWT and gt_begin ------------------------------------------------------------------------

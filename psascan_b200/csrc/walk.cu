@@ -12,15 +12,19 @@
 #include <algorithm>
 #include <vector>
 #include "rank.cuh"
+#include "texthash.cuh"
 
 namespace psc {
 
 // ---- K5 ---------------------------------------------------------------------------------------
+// Every comparison of the binary search looks at most `cap` symbols directly and finishes by fingerprints
+// (texthash.cuh) when they all agree; cap <= 0: symbol by symbol under the work guard.
 __global__ void __launch_bounds__(128)
     initial_ranks_kernel(const uint8_t *__restrict__ block, const uint32_t *__restrict__ sa, long m,
                          const uint8_t *__restrict__ after, long after_len, int after_is_text_end,
                          const uint32_t *__restrict__ gt_after, long gt_after_off, long nstarts,
-                         const uint64_t *__restrict__ starts, uint64_t *__restrict__ out, WorkBudget *wb) {
+                         const uint64_t *__restrict__ starts, uint64_t *__restrict__ out, WorkBudget *wb,
+                         const __grid_constant__ HashView hv, long off_block, long off_after, long cap) {
   long k = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= nstarts) return;
   long st = (long)starts[k];
@@ -33,8 +37,17 @@ __global__ void __launch_bounds__(128)
     long s = sa[mid];
     long slen = m - s;
     long lim = slen < plen ? slen : plen;
-    long lcp = common_prefix_guarded(block + s, pat, lim, wb);
-    if (lcp < 0) { out[k] = 0; return; }  // work guard tripped: the host discards the result
+    long lcp;
+    if (cap <= 0) {
+      lcp = common_prefix_guarded(block + s, pat, lim, wb);
+    } else {
+      lcp = common_prefix(block + s, pat, min(lim, cap));
+      if (lcp == cap && cap < lim) {
+        if (hv.pre) lcp = th_lcp(hv, off_block + s, off_after + st, cap, lim);
+        else { wb->need_hash = 1; lcp = -1; }
+      }
+    }
+    if (lcp < 0) { out[k] = 0; return; }  // guard tripped or fingerprints needed: the host discards the result
     bool pat_greater;
     if (lcp == slen) pat_greater = bit_get(gt_after, gt_after_off + st + slen - 1);  // :66-68
     else if (lcp == plen) pat_greater = false;                                       // :69-71
@@ -50,13 +63,24 @@ void initial_ranks(psc_context *ctx, const uint8_t *block_d, const uint32_t *sa_
                    const uint64_t *starts_d, uint64_t *out_d) {
   PhaseTimer timer(ctx, &ctx->stats.ms_init_ranks);
   if (nstarts <= 0) return;
-  WorkBudget *wb = work_budget_arm(ctx);
-  initial_ranks_kernel<<<(unsigned)div_up(nstarts, 128), 128, 0, ctx->stream>>>(
-      block_d, sa_d, m, after_d, after_len, after_is_text_end, gt_after_bits_d, gt_after_off, nstarts,
-      starts_d, out_d, wb);
-  PSC_LAUNCH_CHECK();
-  ctx->launches++;
-  work_budget_check(ctx, wb, "initial ranks (K5)");
+  const bool contiguous = (after_d == block_d + m) && after_len > 0;
+  long cap = (contiguous && hash_domain_ensure(ctx, block_d, after_d + after_len)) ? lcp_cap() : 0;
+  HashView hv;
+  if (cap > 0) hash_view(ctx, block_d, after_d + after_len, false, &hv);
+  for (int attempt = 0;; ++attempt) {
+    WorkBudget *wb = work_budget_arm(ctx);
+    const long off_block = hv.pre ? (long)(block_d - hv.text) : 0, off_after = hv.pre ? (long)(after_d - hv.text) : 0;
+    initial_ranks_kernel<<<(unsigned)div_up(nstarts, 128), 128, 0, ctx->stream>>>(
+        block_d, sa_d, m, after_d, after_len, after_is_text_end, gt_after_bits_d, gt_after_off, nstarts,
+        starts_d, out_d, wb, hv, off_block, off_after, cap);
+    PSC_LAUNCH_CHECK();
+    ctx->launches++;
+    if (!work_budget_check(ctx, wb, "initial ranks (K5)")) return;
+    if (attempt > 0 || !hash_view(ctx, block_d, after_d + after_len, true, &hv)) {
+      set_error("initial ranks (K5): fingerprints unavailable");
+      throw CudaError{PSC_ECUDA};
+    }
+  }
 }
 
 // ---- K6 ---------------------------------------------------------------------------------------
