@@ -766,10 +766,51 @@ __global__ void __launch_bounds__(256)
   bwt[i] = s ? text[s - 1] : (uint8_t)0;
 }
 
+// The same for blocks that do not fit L2.  The direct gather runs at the random-access rate of the HBM (57 B of
+// DRAM traffic per symbol, profiles/r1_summary.md).  Tried first: a stable split of the pairs (sa[i], i) by text
+// window followed by a gather -- it trades 2^28 random reads for 2^28 single-byte stores and is no faster (count
+// 0.46 + scan 0.92 + split 1.35 + gather 1.69 ms per 256 MiB block against 4.3 ms).  What works is to keep the
+// OUTPUT order: one pass over the SA per text window of 2^26 positions (64 MiB, L2-resident), each pass serving
+// only the entries whose symbol lies in its window.  Reads of the text hit L2, the stores of a warp fall into
+// the same sectors (byte-masked), and the price is reading the SA once per window (4 B x windows per symbol).
+__global__ void __launch_bounds__(256)
+    bwt_window_kernel(const uint8_t *__restrict__ text, const uint32_t *__restrict__ sa, long m, int shift,
+                      uint32_t window, uint8_t *__restrict__ bwt) {
+  const long i = ((long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= m) return;
+  uint32_t s[4];
+  if (i + 4 <= m) {
+    const uint4 v = *reinterpret_cast<const uint4 *>(sa + i);
+    s[0] = v.x; s[1] = v.y; s[2] = v.z; s[3] = v.w;
+  } else {
+    for (int k = 0; k < 4; ++k) s[k] = i + k < m ? sa[i + k] : 0xffffffffu;
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    if (i + k >= m) break;
+    // the symbol before suffix s[k]; the first suffix of the block gets the placeholder 0 (window 0)
+    const uint32_t q = s[k] ? s[k] - 1 : 0u;
+    if ((q >> shift) == window) bwt[i + k] = s[k] ? text[q] : (uint8_t)0;
+  }
+}
+
 void bwt_from_sa(psc_context *ctx, const uint8_t *text_d, const uint32_t *sa_d, long m,
                  uint8_t *bwt_d) {
   PhaseTimer timer(ctx, &ctx->stats.ms_bwt);
   if (m == 0) return;
+  static int shift = -1;  // PSC_BWT_SHIFT: log2 of the window (tests: small windows on small texts)
+  if (shift < 0) { const char *e = getenv("PSC_BWT_SHIFT"); shift = e ? std::max(4, std::min(31, atoi(e))) : 26; }
+  const long nw = ((m - 1) >> shift) + 1;
+  if (nw > 1 && nw <= 64) {
+    KTrace kt(ctx, "bwt(windows)");
+    for (long w = 0; w < nw; ++w) {
+      bwt_window_kernel<<<(unsigned)div_up(div_up(m, 4), 256), 256, 0, ctx->stream>>>(text_d, sa_d, m, shift, (uint32_t)w, bwt_d);
+      PSC_LAUNCH_CHECK();
+    }
+    ctx->launches += nw;
+    return;
+  }
+  KTrace kt(ctx, "bwt(gather)");
   bwt_kernel<<<(unsigned)div_up(m, 256), 256, 0, ctx->stream>>>(text_d, sa_d, m, bwt_d);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
@@ -793,6 +834,7 @@ void gt_begin_from_sa(psc_context *ctx, const uint32_t *sa_d, long m, uint32_t i
   PhaseTimer timer(ctx, &ctx->stats.ms_bwt);
   long cnt = m - 1 - (long)i0;
   if (cnt <= 0) return;
+  KTrace kt(ctx, "gt_begin");
   gt_begin_kernel<<<(unsigned)div_up(cnt, 256), 256, 0, ctx->stream>>>(sa_d, m, i0, bits_d, bit_off);
   PSC_LAUNCH_CHECK();
   ctx->launches++;

@@ -291,10 +291,10 @@ def test_dist_schedule_single_rank(ctx):
 
 
 @pytest.mark.parametrize("env", [dict(PSC_WALK_MODE="1"), dict(PSC_WALK_MODE="2"), dict(PSC_WALK_CHUNK="4096"),
-                                 dict(PSC_WALKERS="7"), dict(PSC_MERGE_CHUNK="1000"),
+                                 dict(PSC_WALKERS="7"), dict(PSC_MERGE_CHUNK="1000"), dict(PSC_BWT_SHIFT="8"),
                                  dict(PSC_MERGE_CHUNK="64", PSC_WALK_CHUNK="2048", PSC_WALK_MODE="2")],
                          ids=["walk_warp_aggregated", "walk_emit_partition", "walk_multi_chunk", "seven_walkers",
-                              "merge_small_chunks", "all_small"])
+                              "merge_small_chunks", "bwt_windowed", "all_small"])
 def test_env_selected_paths_subprocess(env):
     """Paths chosen by environment variables read once per process (the warp-aggregated and the
     emit + partition walk, tails cut into several walk chunks, a handful of walkers, the final merge in
@@ -441,6 +441,10 @@ def test_config2_full_size_verified(ctx):
     # and the same text in 5 ragged blocks: rank planes of 255 symbols, gap arrays, the merge by output range
     ctx.construct_sa_ptr(text.data_ptr(), 1 << 28, out.data_ptr(), (1 << 26) - 12345, device=True)
     assert ctx.stats()["n_blocks"] == 5
+    assert ctx.verify_sa_ptr(text.data_ptr(), 1 << 28, out.data_ptr()) == [0, 0, 0, 0]
+    # 3 ragged blocks of ~128 MiB: the BWT in passes over 64 MiB text windows (sufsort.cu, 2 full + 1 ragged)
+    ctx.construct_sa_ptr(text.data_ptr(), 1 << 28, out.data_ptr(), (1 << 27) - 12345, device=True)
+    assert ctx.stats()["n_blocks"] == 3
     assert ctx.verify_sa_ptr(text.data_ptr(), 1 << 28, out.data_ptr()) == [0, 0, 0, 0]
     del text, out
     torch.cuda.empty_cache()
