@@ -38,6 +38,7 @@ typedef struct psc_rank psc_rank;       /* device rank structure over one block 
 
 const char *psc_last_error(void);
 int psc_version(void);
+int psc_device_count(void); /* visible CUDA devices (0 when there is none or no driver) */
 
 /* Device / stream setup; nothing in the reference corresponds (psascan.hpp:53-131 only
  * budgets host RAM).  device < 0: current device.  hbm_budget = 0: all free memory. */

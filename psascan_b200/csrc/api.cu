@@ -346,7 +346,12 @@ using namespace psc;
 extern "C" {
 
 const char *psc_last_error(void) { return g_err; }
-int psc_version(void) { return 100; }
+int psc_version(void) { return 200; }
+int psc_device_count(void) {
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return count;
+}
 
 int psc_init(int device, size_t hbm_budget, psc_context **out) {
   if (!out) { set_error("psc_init: null out pointer"); return PSC_EARG; }

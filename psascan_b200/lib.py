@@ -7,7 +7,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 EXPORTS = [
-    "psc_last_error", "psc_version", "psc_init", "psc_shutdown", "psc_max_block_size",
+    "psc_last_error", "psc_version", "psc_device_count", "psc_init", "psc_shutdown", "psc_max_block_size",
     "psc_sort_block", "psc_rank_build", "psc_rank_counts", "psc_rank_query", "psc_rank_free",
     "psc_initial_ranks", "psc_compute_gap", "psc_merge_level", "psc_gap_to_bitvector",
     "psc_merge_bwt", "psc_split_gap", "psc_construct_sa", "psc_construct_sa_d", "psc_get_stats",

@@ -65,3 +65,33 @@ def test_cli_rejects_255(cli, tmp_path):
     f.write_bytes(b"abc\xffdef" * 50)
     r = run(cli, [str(f)])
     assert r.returncode == 1 and "byte with value 255 was detected in the input text!" in r.stdout
+
+
+@pytest.mark.gpu
+def test_cli_all_visible_gpus(cli, tmp_path):
+    """construct_sa uses every visible GPU for a text of several blocks (one host thread per GPU inside one
+    process, NCCL set up by the library); the file must equal the golden .sa5 whatever the GPU count.
+    PSASCAN_GPUS=1 pins the single-GPU pipeline on the same input."""
+    import torch
+    ngpu = torch.cuda.device_count()
+    for name, gen, kw, n, sa5 in golden_cases()[-3:]:
+        f = tmp_path / (name + ".txt")
+        golden_text(gen, kw, n).tofile(str(f))
+        for env in ({"PSASCAN_MAX_BLOCK": str(n // 5 + 3)}, {"PSASCAN_MAX_BLOCK": "1000", "PSASCAN_GPUS": "1"},
+                    {"PSASCAN_MAX_BLOCK": str(n // 2 + 1), "PSASCAN_GPUS": "2"}):
+            out = tmp_path / (name + ".out")
+            if out.exists():
+                out.unlink()
+            r = run(cli, [str(f), "-o", str(out)], env=env)
+            assert r.returncode == 0, r.stderr[-2000:]
+            assert np.array_equal(np.fromfile(str(out), dtype=np.uint8), sa5), (name, env)
+            want = min(ngpu, int(env.get("PSASCAN_GPUS", ngpu)), -(-n // int(env["PSASCAN_MAX_BLOCK"])))
+            assert ("GPU = %d x" % want) in r.stderr, r.stderr[:600]
+
+
+def test_cli_memory_error_text(cli, tmp_path):
+    """ram_use below 6 bytes: the reference's message and exit status (psascan.hpp:57-60)"""
+    f = tmp_path / "t.txt"
+    f.write_bytes(b"banana")
+    r = run(cli, [str(f), "-m", "5"])
+    assert r.returncode == 1 and "Error: not enough memory to run pSAscan." in r.stderr
