@@ -162,7 +162,11 @@ inline void pSAscan_impl(const std::string &input_filename, const std::string &o
         if (r.rc == PSC_OK)
           r.rc = psc_construct_sa_dist_slice_d(r.ctx, (const uint8_t *)r.text_d, n, max_block, (uint8_t *)r.out_d,
                                                &r.slice_beg, &r.slice_len);
-        if (r.rc != PSC_OK) r.err = psc_last_error();  // the message is per thread
+        if (r.rc != PSC_OK) {
+          r.err = psc_last_error();  // the message is per thread
+          for (int h = 0; h < n_gpus; ++h)
+            if (h != g) psc_dist_abort(gpu[h].ctx);  // the others must not wait for this rank
+        }
       });
     for (auto &t : th) t.join();
   }

@@ -141,6 +141,8 @@ int psc_construct_sa_d(psc_context *ctx, const uint8_t *text_d, long n, long max
  *                        by any means (torch.distributed, MPI, a shared variable)
  *   psc_dist_init        collective: ncclCommInitRank on the context's device; world == 1 needs no id
  *   psc_dist_finalize    destroys the communicator (psc_shutdown does not)
+ *   psc_dist_abort       callable from any thread when a rank has failed: the collectives the other ranks
+ *                        wait in end with an error (ncclCommAbort) instead of hanging
  * Schedule (csrc/dist.cu): blocks are sorted on separate GPUs (rank r owns blocks B-1-r, B-1-r-world, ...);
  * per block the owner broadcasts the BWT, gt bits and the walkers' start ranks (the block SA stays with its
  * owner), every GPU walks a contiguous share of the tail against the replicated rank structure, the per-GPU
@@ -154,6 +156,7 @@ int psc_construct_sa_d(psc_context *ctx, const uint8_t *text_d, long n, long max
 int psc_dist_unique_id(uint8_t id[128]);
 int psc_dist_init(psc_context *ctx, const uint8_t id[128], int rank, int world);
 int psc_dist_finalize(psc_context *ctx);
+int psc_dist_abort(psc_context *ctx);
 int psc_construct_sa_dist_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block, uint8_t *out_sa5_d);
 int psc_construct_sa_dist_slice_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
                                   uint8_t *out_slice_sa5_d, long *slice_beg, long *slice_len);

@@ -14,6 +14,7 @@ struct NcclApi {
   ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
   ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*CommAbort)(ncclComm_t) = nullptr;
   const char *(*GetErrorString)(ncclResult_t) = nullptr;
   ncclResult_t (*Broadcast)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*ReduceScatter)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
@@ -53,7 +54,7 @@ bool nccl_load() {
   }
   if (!g_nccl.handle) { set_error("cannot open libnccl: %s", dlerror()); return false; }
   bool ok = sym(g_nccl.GetUniqueId, "ncclGetUniqueId") && sym(g_nccl.CommInitRank, "ncclCommInitRank") &&
-            sym(g_nccl.CommDestroy, "ncclCommDestroy") && sym(g_nccl.GetErrorString, "ncclGetErrorString") &&
+            sym(g_nccl.CommDestroy, "ncclCommDestroy") && sym(g_nccl.CommAbort, "ncclCommAbort") && sym(g_nccl.GetErrorString, "ncclGetErrorString") &&
             sym(g_nccl.Broadcast, "ncclBroadcast") && sym(g_nccl.ReduceScatter, "ncclReduceScatter") &&
             sym(g_nccl.AllGather, "ncclAllGather") && sym(g_nccl.AllReduce, "ncclAllReduce") &&
             sym(g_nccl.Send, "ncclSend") && sym(g_nccl.Recv, "ncclRecv") && sym(g_nccl.GroupStart, "ncclGroupStart") &&
@@ -84,6 +85,14 @@ int nccl_comm_init(Comm *c, const uint8_t id[128], int rank, int world) {
   if (r != ncclSuccess) { set_error("ncclCommInitRank(rank %d of %d): %s", rank, world, g_nccl.GetErrorString(r)); return PSC_ECUDA; }
   c->nccl = comm;
   return PSC_OK;
+}
+
+// any thread may call this: outstanding collectives of the communicator end with an error instead of waiting
+// for a rank that has failed
+void nccl_comm_abort(Comm *c) {
+  void *h = c->nccl;
+  c->nccl = nullptr;
+  if (h && g_nccl.CommAbort) g_nccl.CommAbort((ncclComm_t)h);
 }
 
 void nccl_comm_destroy(Comm *c) {

@@ -32,5 +32,6 @@ bool nccl_load();            // false + set_error when libnccl cannot be opened
 int nccl_unique_id(uint8_t id[128]);
 int nccl_comm_init(Comm *c, const uint8_t id[128], int rank, int world);
 void nccl_comm_destroy(Comm *c);
+void nccl_comm_abort(Comm *c);
 
 }  // namespace psc

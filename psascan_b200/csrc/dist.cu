@@ -434,6 +434,11 @@ int psc_dist_finalize(psc_context *ctx) {
   return PSC_OK;
 }
 
+int psc_dist_abort(psc_context *ctx) {
+  if (ctx && ctx->comm) nccl_comm_abort(ctx->comm);
+  return PSC_OK;
+}
+
 int psc_dist_stats(psc_context *ctx, long *n_collectives, double *bytes) {
   if (!ctx || !ctx->comm) { set_error("psc_dist_stats: psc_dist_init has not been called"); return PSC_EARG; }
   if (n_collectives) *n_collectives = ctx->comm->n_calls;

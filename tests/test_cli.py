@@ -20,7 +20,7 @@ def cli():
 def run(cli, args, stdin=None, env=None):
     e = dict(os.environ)
     e.update(env or {})
-    return subprocess.run([cli] + args, input=stdin, capture_output=True, text=True, env=e)
+    return subprocess.run([cli] + args, input=stdin, capture_output=True, text=True, env=e, timeout=240)
 
 
 def test_cli_argument_errors(cli, tmp_path):
