@@ -206,6 +206,17 @@ long psc_verify_noalloc_max_n(void);
 int psc_verify_sa_noalloc_d(psc_context *ctx, const uint8_t *text_d, long n, const uint8_t *sa5_d,
                             long violations[4]);
 
+/* ---- by-products, all on device buffers.
+ * psc_delete_sentinel_bytes_d: tools/delete-sentinel-bytes/src/main.cpp:45-104 -- out_d receives the bytes of
+ *   in_d[n] that are not 255, in order (out_d must hold n bytes); *n_out = how many.
+ * psc_bwt_from_sa5_d: full-text BWT from the finished suffix array, bwt[i] = text[sa[i] - 1]; the row of suffix 0
+ *   holds byte 0 and its index is returned in *i0 (the convention of inmem_bwt_from_sa.hpp:48-56).
+ * psc_isa_samples_d: samples_d[p / rate] = i for every i with sa[i] = p, p a multiple of rate
+ *   (samples_d holds (n - 1) / rate + 1 entries). */
+int psc_delete_sentinel_bytes_d(psc_context *ctx, const uint8_t *in_d, long n, uint8_t *out_d, long *n_out);
+int psc_bwt_from_sa5_d(psc_context *ctx, const uint8_t *text_d, long n, const uint8_t *sa5_d, uint8_t *bwt_d, long *i0);
+int psc_isa_samples_d(psc_context *ctx, const uint8_t *sa5_d, long n, long rate, uint64_t *samples_d);
+
 /* micro-benchmarks used for the roofline denominators (SURVEY.md 8-d "R32") */
 int psc_bench_random_sectors(psc_context *ctx, size_t bytes, int iters, double *gbs);
 int psc_bench_radix_pass(psc_context *ctx, long n, int iters, double *ms_per_pass);

@@ -15,7 +15,8 @@ EXPORTS = [
     "psc_pinned_alloc", "psc_pinned_free", "psc_copy_h2d", "psc_copy_d2h", "psc_device_info", "psc_construct_sa_dist_d",
     "psc_construct_sa_dist_slice_d", "psc_dist_slice_capacity", "psc_verify_sa_d",
     "psc_verify_sa_noalloc_d", "psc_verify_noalloc_max_n", "psc_dist_unique_id", "psc_dist_init",
-    "psc_dist_finalize", "psc_dist_stats", "psc_dist_abort",
+    "psc_dist_finalize", "psc_dist_stats", "psc_dist_abort", "psc_delete_sentinel_bytes_d",
+    "psc_bwt_from_sa5_d", "psc_isa_samples_d",
 ]
 
 
