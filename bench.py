@@ -429,21 +429,22 @@ def main():
     # ---- verification of what the timed loops produced (untimed): e2e result and device result
     step_dev()
     if sharded:
-        full = torch.empty(5 * n, dtype=torch.uint8, device="cuda") if rank == 0 else None
-        for h in range(world):
-            hb, he = pdist.share_begin(h, n, world), pdist.share_begin(h + 1, n, world)
-            if he <= hb:
-                continue
-            if rank == 0:
-                if h == 0:
-                    full[5 * hb:5 * he].copy_(dev_out[:5 * (he - hb)])
-                else:
-                    dist.recv(full[5 * hb:5 * he], src=h)
-            elif rank == h:
-                dist.send(dev_out[:5 * (he - hb)], dst=0)
-        viol = ctx.verify_sa_ptr(dev_text.data_ptr(), n, full.data_ptr()) if rank == 0 else [0, 0, 0, 0]
+        # every rank checks its own slice (range + strict suffix order of adjacent entries, psc_verify_sa_slice_d);
+        # the pair across a slice boundary needs the first entry of the next slice
+        first = torch.zeros(8, dtype=torch.uint8, device="cuda")
+        if share[1] > 0:
+            first[:5] = dev_out[:5]
+        firsts = [torch.zeros(8, dtype=torch.uint8, device="cuda") for _ in range(world)]
+        dist.all_gather(firsts, first)
+        lens = [pdist.share_begin(h + 1, n, world) - pdist.share_begin(h, n, world) for h in range(world)]
+        nxt = -1
+        for h in range(rank + 1, world):
+            if lens[h] > 0:
+                nxt = int.from_bytes(bytes(firsts[h][:5].cpu().tolist()), "little")
+                break
+        v2 = ctx.verify_sa_slice_ptr(dev_text.data_ptr(), n, dev_out.data_ptr(), share[0], share[1], nxt)
+        viol = [v2[0], 0, 0, v2[1]]
         e2e_same = bool(torch.equal(host_out[:5 * share[1]], dev_out[:5 * share[1]].cpu()))
-        del full
     else:
         viol = ctx.verify_sa_ptr(dev_text.data_ptr(), n, dev_out.data_ptr())
         e2e_same = bool(torch.equal(host_out, dev_out.cpu())) if n <= (1 << 32) else True
@@ -471,7 +472,8 @@ def main():
                         "d2h_bytes_per_step": 5 * n, "ms_per_step": e2e_ms / a.steps},
                 "gpu_launches": s["kernel_launches"] * a.steps, "comm_per_step": comm,
                 "verified": verified, "verify": {"violations": viol, "e2e_equals_device_result": e2e_same,
-                                                 "how": "psc_verify_sa_d: permutation + first-symbol order + tie order via ISA"},
+                                                 "how": ("psc_verify_sa_slice_d on every rank: entries in range + adjacent suffixes in strictly increasing order"
+                                                         if sharded else "psc_verify_sa_d: permutation + first-symbol order + tie order via ISA")},
                 "phases_ms": {k: s[k] for k in s if k.startswith("ms_")},
                 "counters": {k: s[k] for k in s if not k.startswith("ms_")}}
         if s["lf_steps"] > 0:

@@ -193,6 +193,14 @@ int psc_device_info(psc_context *ctx, char *name, size_t name_len, size_t *free_
  * All four zero <=> out_sa5_d is THE suffix array of text_d.  n < 2^32 - 1 (4 n bytes of scratch). */
 int psc_verify_sa_d(psc_context *ctx, const uint8_t *text_d, long n, const uint8_t *sa5_d, long violations[4]);
 
+/* Check of a SLICE of a suffix array: entries [slice_beg, slice_beg + slice_len) in slice_sa5_d and next_first =
+ * entry slice_beg + slice_len (ignored for the last slice).  violations[0] = entries >= n, [1] = adjacent pairs
+ * whose suffixes are not in strictly increasing order (compared directly; long common prefixes by fingerprints).
+ * All slices clean <=> the array is the suffix array.  Works for any n and needs no exchange between the GPUs that
+ * hold the slices (psc_construct_sa_dist_slice_d). */
+int psc_verify_sa_slice_d(psc_context *ctx, const uint8_t *text_d, long n, const uint8_t *slice_sa5_d, long slice_beg,
+                          long slice_len, long next_first, long violations[2]);
+
 /* The same check for callers that must not allocate (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid cudaMalloc).  No counterpart in the reference.
  * The scratch (inverse array + counters) is a static device array inside the library, 16 MiB + 256

@@ -266,6 +266,19 @@ static void dist_merge(psc_context *ctx, Comm &cm, long n, long max_block, long 
   std::vector<uint64_t> tot((size_t)B * world);
   d2h(ctx, tot.data(), totals_d.p, tot.size());
   sync(ctx);
+  // gap counters are uint32 (the reference keeps 1 byte + an excess list, gap_array.hpp:63, 79-88): the counters
+  // of block k must add up to the length of its tail, else one of them has wrapped around (a text in which more
+  // than 2^32 - 1 tail suffixes fall between two neighbouring block suffixes)
+  for (long k = 0; k + 1 < B; ++k) {
+    uint64_t sum = 0;
+    for (int h = 0; h < world; ++h) sum += tot[(size_t)h * B + k];
+    const uint64_t tail = (uint64_t)(n - std::min(n, (k + 1) * max_block));
+    if (sum != tail) {
+      set_error("gap counters of block %ld add up to %llu, its tail has %llu suffixes: a 32-bit counter overflowed", k,
+                (unsigned long long)sum, (unsigned long long)tail);
+      throw CudaError{PSC_ELIMIT};
+    }
+  }
   // split: level by level, every rank answers from its gap slices, answers are summed
   MergePlan plan;
   plan.resize((int)B, nb);

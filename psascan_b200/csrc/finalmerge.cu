@@ -160,6 +160,7 @@ void final_merge_resident(psc_context *ctx, const std::vector<MergePiece> &pc, l
     KTrace kt(ctx, "merge_split");
     DevBuf<uint64_t> tab(ctx, (size_t)3 * B * nb);
     uint64_t *Qd = tab.p, *Ud = tab.p + (size_t)B * nb, *Ed = tab.p + (size_t)2 * B * nb;
+    DevBuf<uint64_t> sums(ctx, B);  // sum of every block's gap counters
     h2d(ctx, Qd, plan.q.data(), nb);
     for (int k = 0; k < B; ++k) {
       uint64_t *qk = Qd + (size_t)k * nb, *uk = Ud + (size_t)k * nb, *ek = Ed + (size_t)k * nb;
@@ -171,13 +172,25 @@ void final_merge_resident(psc_context *ctx, const std::vector<MergePiece> &pc, l
       const long cnt = pc[k].m + 1;
       DevBuf<uint64_t> carry(ctx, coarse_carry_tiles(cnt) + 1);
       coarse_carries_u32(ctx, pc[k].gap, cnt, carry.p);
+      PSC_CUDA(cudaMemcpyAsync(sums.p + k, carry.p + coarse_carry_tiles(cnt), 8, cudaMemcpyDeviceToDevice, ctx->stream));
       merge_split_slice(ctx, pc[k].gap, cnt, 0, 0, carry.p, true, qk, nb, uk, ek);
       merge_split_next(ctx, qk, uk, nb, qk + nb);
     }
     d2h(ctx, plan.q.data(), Qd, (size_t)B * nb);
     d2h(ctx, plan.u.data(), Ud, (size_t)B * nb);
     d2h(ctx, plan.e.data(), Ed, (size_t)B * nb);
+    std::vector<uint64_t> hs(B, 0);
+    d2h(ctx, hs.data(), sums.p, (size_t)(B - 1));
     sync(ctx);
+    // uint32 counters (the reference: 1 byte + excess list, gap_array.hpp:63, 79-88) must add up to the tail length
+    for (int k = 0; k + 1 < B; ++k) {
+      const uint64_t tail = (uint64_t)(n - (pc[k].beg + pc[k].m));
+      if (hs[k] != tail) {
+        set_error("gap counters of block %d add up to %llu, its tail has %llu suffixes: a 32-bit counter overflowed", k,
+                  (unsigned long long)hs[k], (unsigned long long)tail);
+        throw CudaError{PSC_ELIMIT};
+      }
+    }
   }
   MergeScratch scr;
   scr.reserve(ctx, std::min(n, C) + 16, need_hi_plane(n));

@@ -4,6 +4,7 @@
 // symbol are ordered like the suffixes that follow them (through the inverse array).  Used by
 // bench.py after the timed loop and by the parity tests at sizes no CPU sorter reaches.
 #include "common.cuh"
+#include "texthash.cuh"
 
 namespace psc {
 
@@ -65,6 +66,72 @@ extern "C" int psc_verify_sa_d(psc_context *ctx, const uint8_t *text_d, long n, 
     d2h(ctx, h, viol.p, 4);
     sync(ctx);
     for (int k = 0; k < 4; ++k) violations[k] = (long)h[k];
+    return PSC_OK;
+  } catch (const CudaError &e) { return e.code; }
+}
+
+// ---- check of a SLICE of a suffix array, for arrays spread over several GPUs and texts beyond 2^32 ----------
+// Entries [slice_beg, slice_beg + slice_len) as 5-byte values, plus the first entry of the next slice.  Checked:
+// every entry < n, and suffix(sa[i]) < suffix(sa[i+1]) for every adjacent pair, by comparing the two suffixes
+// directly (at most PSC_LCP_CAP symbols, then fingerprints: texthash.cuh).  n in-range entries in strictly
+// increasing suffix order are all different, hence a permutation, hence THE suffix array: no inverse array, no
+// exchange between the ranks.  violations[0] = entries >= n, [1] = adjacent pairs out of order.
+__global__ void __launch_bounds__(256)
+    verify_slice_kernel(const uint8_t *__restrict__ text, long n, const uint8_t *__restrict__ sa5, long len,
+                        long next_first, unsigned long long *__restrict__ viol, WorkBudget *wb,
+                        const __grid_constant__ HashView hv, long cap) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= len) return;
+  const uint64_t a = load_sa5(sa5, i);
+  if (a >= (uint64_t)n) { atomicAdd(&viol[0], 1ull); return; }
+  long b = i + 1 < len ? (long)load_sa5(sa5, i + 1) : next_first;
+  if (b < 0) return;                       // the very last entry of the array
+  if (b >= n) return;                      // counted by its own thread (or by the next slice)
+  if ((long)a == b) { atomicAdd(&viol[1], 1ull); return; }
+  const long lim = n - max((long)a, b);
+  long el = common_prefix(text + a, text + b, min(lim, cap));
+  if (el == cap && cap < lim) {
+    if (hv.pre) el = th_lcp(hv, (long)a, b, cap, lim);
+    else { wb->need_hash = 1; return; }
+  }
+  // one suffix is a prefix of the other: the shorter one (the later position) is the smaller
+  const bool ordered = el == lim ? ((long)a > b) : (text[a + el] < text[b + el]);
+  if (!ordered) atomicAdd(&viol[1], 1ull);
+}
+
+extern "C" int psc_verify_sa_slice_d(psc_context *ctx, const uint8_t *text_d, long n, const uint8_t *slice_sa5_d,
+                                     long slice_beg, long slice_len, long next_first, long violations[2]) {
+  try {
+    if (!ctx || n < 0 || !violations || slice_beg < 0 || slice_len < 0 || slice_beg + slice_len > n ||
+        (slice_len > 0 && (!text_d || !slice_sa5_d)) || (slice_beg + slice_len < n && next_first < 0)) {
+      set_error("psc_verify_sa_slice_d: bad argument");
+      return PSC_EARG;
+    }
+    violations[0] = violations[1] = 0;
+    if (slice_len == 0) return PSC_OK;
+    PSC_CUDA(cudaSetDevice(ctx->device));
+    hash_domain_set(ctx, text_d, n);
+    struct DomainGuard { psc_context *c; ~DomainGuard() { hash_domain_clear(c); } } domain_guard{ctx};
+    const long cap = ((uintptr_t)text_d & 15) == 0 ? lcp_cap() : (1L << 62);  // unaligned text: symbol by symbol
+    HashView hv;
+    DevBuf<unsigned long long> viol(ctx, 2);
+    for (int attempt = 0;; ++attempt) {
+      viol.zero();
+      WorkBudget *wb = work_budget_arm(ctx);
+      verify_slice_kernel<<<(unsigned)div_up(slice_len, 256), 256, 0, ctx->stream>>>(
+          text_d, n, slice_sa5_d, slice_len, slice_beg + slice_len < n ? next_first : -1, viol.p, wb, hv, cap);
+      PSC_LAUNCH_CHECK();
+      if (!work_budget_check(ctx, wb, "verify")) break;
+      if (attempt > 0 || !hash_view(ctx, text_d, text_d + n, true, &hv)) {
+        set_error("psc_verify_sa_slice_d: fingerprints unavailable");
+        return PSC_ECUDA;
+      }
+    }
+    unsigned long long h[2];
+    d2h(ctx, h, viol.p, 2);
+    sync(ctx);
+    violations[0] = (long)h[0];
+    violations[1] = (long)h[1];
     return PSC_OK;
   } catch (const CudaError &e) { return e.code; }
 }

@@ -16,7 +16,7 @@ EXPORTS = [
     "psc_construct_sa_dist_slice_d", "psc_dist_slice_capacity", "psc_verify_sa_d",
     "psc_verify_sa_noalloc_d", "psc_verify_noalloc_max_n", "psc_dist_unique_id", "psc_dist_init",
     "psc_dist_finalize", "psc_dist_stats", "psc_dist_abort", "psc_delete_sentinel_bytes_d",
-    "psc_bwt_from_sa5_d", "psc_isa_samples_d",
+    "psc_bwt_from_sa5_d", "psc_isa_samples_d", "psc_verify_sa_slice_d",
 ]
 
 
@@ -234,6 +234,13 @@ class Context:
         """O(n) device check (psc_verify_sa_d): returns the four violation counts, all zero for a correct SA"""
         v = (C.c_long * 4)()
         self._chk(self.lib.psc_verify_sa_d(self.h, C.c_void_p(text_dev_ptr), C.c_long(n), C.c_void_p(sa5_dev_ptr), v))
+        return [int(x) for x in v]
+
+    def verify_sa_slice_ptr(self, text_dev_ptr, n, slice_dev_ptr, slice_beg, slice_len, next_first=-1):
+        """psc_verify_sa_slice_d: [entries >= n, adjacent pairs out of suffix order] for one slice of the SA"""
+        v = (C.c_long * 2)()
+        self._chk(self.lib.psc_verify_sa_slice_d(self.h, C.c_void_p(text_dev_ptr), C.c_long(n), C.c_void_p(slice_dev_ptr),
+                                                 C.c_long(slice_beg), C.c_long(slice_len), C.c_long(next_first), v))
         return [int(x) for x in v]
 
     def verify_sa_noalloc_ptr(self, text_dev_ptr, n, sa5_dev_ptr):

@@ -508,3 +508,33 @@ def test_periodic_texts_across_block_boundaries_bounded():
         "print('periodic ok')\n")
     r = _run_child(code, dict(PSC_COMPARE_BUDGET=str(1 << 36)), timeout=3000)
     assert r.returncode == 0 and "periodic ok" in r.stdout, (r.stdout[-800:], r.stderr[-2500:])
+
+
+def test_verify_sa_slices(ctx):
+    """psc_verify_sa_slice_d: slices of a correct suffix array are clean (also on a periodic text whose adjacent
+    suffixes share prefixes far beyond the direct-compare cap), every kind of damage is counted, and the slice
+    boundary pair is checked through next_first."""
+    import torch
+    for text in (textgen.markov(60000, seed=41), textgen.periodic(40000, period=13, sigma=2), np.zeros(5000, dtype=np.uint8)):
+        n = len(text)
+        sa5 = ctx.construct_sa(text, max_block=n // 3 + 1)
+        sa = decode_sa5(sa5)
+        d_text = torch.from_numpy(text).cuda()
+
+        def check(arr, beg, ln):
+            d = torch.from_numpy(O.encode_uint40(arr[beg:beg + ln])).cuda()
+            nxt = int(arr[beg + ln]) if beg + ln < n else -1
+            return ctx.verify_sa_slice_ptr(d_text.data_ptr(), n, d.data_ptr(), beg, ln, nxt)
+
+        cuts = [0, n // 3, n // 3 + 1, 2 * n // 3, n]
+        for a, b in zip(cuts, cuts[1:]):
+            assert check(sa, a, b - a) == [0, 0], (n, a, b)
+        bad = sa.copy(); bad[7] = n + 1
+        assert check(bad, 0, n // 3)[0] == 1
+        bad = sa.copy(); bad[100], bad[101] = bad[101], bad[100]
+        assert check(bad, 0, n // 3)[1] >= 1
+        bad = sa.copy(); bad[500] = bad[499]
+        assert check(bad, 0, n)[1] >= 1
+        k = n // 3   # damage exactly at a slice boundary: only next_first can see it
+        bad = sa.copy(); bad[k - 1], bad[k] = bad[k], bad[k - 1]
+        assert check(bad, 0, k)[1] + check(bad, k, n - k)[1] >= 1
