@@ -390,8 +390,13 @@ def main():
         return ctx.stats()
 
     def step_e2e():
-        if sharded:   # host text -> HBM on every rank, sharded construction, every rank's slice back to its host
-            dev_text.copy_(host_text, non_blocking=True)
+        if sharded:   # the text crosses PCIe once in total: every rank uploads 1/N of it, NVLink all-gather completes it
+            if n % world == 0:
+                per = n // world
+                dev_text[rank * per:(rank + 1) * per].copy_(host_text[rank * per:(rank + 1) * per], non_blocking=True)
+                dist.all_gather_into_tensor(dev_text, dev_text[rank * per:(rank + 1) * per])
+            else:
+                dev_text.copy_(host_text, non_blocking=True)
             torch.cuda.synchronize()
             _, ln, _ = pdist.construct_sa_slices(ctx, dev_text.data_ptr(), n, dev_out.data_ptr(), max_block)
             host_out[:5 * ln].copy_(dev_out[:5 * ln], non_blocking=True)
@@ -468,7 +473,7 @@ def main():
                                                     "merge by output range; every rank keeps n/N of the SA"
                                                     if sharded else "single GPU"), max_block=max_block, n_blocks=s["n_blocks"]),
                 "clocks": clocks, "wall_ms_per_step": wall_ms / a.steps,
-                "e2e": {"value": e2e, "unit": "MB/s", "h2d_bytes_per_step": n * world if sharded else n,
+                "e2e": {"value": e2e, "unit": "MB/s", "h2d_bytes_per_step": n if (not sharded or n % world == 0) else n * world,
                         "d2h_bytes_per_step": 5 * n, "ms_per_step": e2e_ms / a.steps},
                 "gpu_launches": s["kernel_launches"] * a.steps, "comm_per_step": comm,
                 "verified": verified, "verify": {"violations": viol, "e2e_equals_device_result": e2e_same,
