@@ -116,6 +116,22 @@ void Comm::reduce_scatter_u32(psc_context *ctx, const uint32_t *send_d, uint32_t
   n_calls++; bytes += (double)per * 4 * world;
 }
 
+void Comm::reduce_scatter_u8(psc_context *ctx, const uint8_t *send_d, uint8_t *recv_d, size_t per) {
+  if (per == 0) return;
+  if (world == 1) {
+    if (recv_d != send_d) PSC_CUDA(cudaMemcpyAsync(recv_d, send_d, per, cudaMemcpyDeviceToDevice, ctx->stream));
+    return;
+  }
+  check(g_nccl.ReduceScatter(send_d, recv_d, per, ncclUint8, ncclSum, (ncclComm_t)nccl, ctx->stream), "ncclReduceScatter(u8)");
+  n_calls++; bytes += (double)per * world;
+}
+
+void Comm::allreduce_max_u32(psc_context *ctx, uint32_t *buf_d, size_t count) {
+  if (world == 1 || count == 0) return;
+  check(g_nccl.AllReduce(buf_d, buf_d, count, ncclUint32, ncclMax, (ncclComm_t)nccl, ctx->stream), "ncclAllReduce(max)");
+  n_calls++; bytes += (double)count * 4;
+}
+
 void Comm::allgather(psc_context *ctx, const void *send_d, void *recv_d, size_t bytes_per) {
   if (bytes_per == 0) return;
   if (world == 1) {

@@ -17,6 +17,8 @@ struct Comm {
   void bcast(psc_context *ctx, void *buf_d, size_t bytes, int root);
   // recv_d[0 .. per) = sum over ranks of their send_d[rank * per .. (rank + 1) * per)
   void reduce_scatter_u32(psc_context *ctx, const uint32_t *send_d, uint32_t *recv_d, size_t per);
+  void reduce_scatter_u8(psc_context *ctx, const uint8_t *send_d, uint8_t *recv_d, size_t per);  // sums must stay < 256
+  void allreduce_max_u32(psc_context *ctx, uint32_t *buf_d, size_t count);
   // recv_d[g * bytes_per .. ) = rank g's send_d; in place allowed when send_d == recv_d + rank * bytes_per
   void allgather(psc_context *ctx, const void *send_d, void *recv_d, size_t bytes_per);
   void allreduce_sum_u64(psc_context *ctx, uint64_t *buf_d, size_t count);

@@ -43,6 +43,29 @@ __global__ void or_bits_shifted_kernel(uint32_t *dst, long dst_off, const uint32
 
 __global__ void set_bit_kernel(uint32_t *dst, long idx) { atomicOr(&dst[idx >> 5], 1u << (idx & 31)); }
 
+// Gap counters travel as bytes when they are small enough (they almost always are: a rank's counts of one block
+// average below one per entry): 4 entries per thread, the largest value seen goes to *vmax.
+__global__ void __launch_bounds__(256)
+    narrow_u32_to_u8_kernel(const uint32_t *__restrict__ in, long n4, uint32_t *__restrict__ out4, uint32_t *vmax) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t mx = 0;
+  if (i < n4) {
+    const uint4 v = reinterpret_cast<const uint4 *>(in)[i];
+    mx = max(max(v.x, v.y), max(v.z, v.w));
+    out4[i] = (v.x & 255u) | ((v.y & 255u) << 8) | ((v.z & 255u) << 16) | (v.w << 24);
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((threadIdx.x & 31) == 0 && mx) atomicMax(vmax, mx);
+}
+__global__ void __launch_bounds__(256)
+    widen_u8_to_u32_kernel(const uint32_t *__restrict__ in4, long n4, uint32_t *__restrict__ out) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n4) return;
+  const uint32_t v = in4[i];
+  reinterpret_cast<uint4 *>(out)[i] = make_uint4(v & 255u, (v >> 8) & 255u, (v >> 16) & 255u, v >> 24);
+}
+
 struct OwnedBlock {
   DevBuf<uint32_t> sa;
   DevBuf<uint8_t> bwt;
@@ -219,7 +242,28 @@ static void dist_blocks(psc_context *ctx, Comm &cm, const uint8_t *text_d, long 
       rank_free(rk);
       // per-GPU gap counts summed, every rank keeps a slice
       pcs.gap[id].alloc(ctx, per);
-      cm.reduce_scatter_u32(ctx, gap_full.p, pcs.gap[id].p, (size_t)per);
+      bool as_bytes = false;
+      if (world > 1 && !getenv("PSC_GAP_RS32")) {
+        // 1 byte per counter over NVLink instead of 4 when no sum can reach 256 (largest local count * ranks < 256)
+        DevBuf<uint8_t> narrow(ctx, (size_t)per * world), slice8(ctx, per);
+        DevBuf<uint32_t> vmax(ctx, 1);
+        vmax.zero();
+        const long n4 = per * world / 4;
+        narrow_u32_to_u8_kernel<<<(unsigned)div_up(n4, 256), 256, 0, ctx->stream>>>(gap_full.p, n4, reinterpret_cast<uint32_t *>(narrow.p), vmax.p);
+        PSC_LAUNCH_CHECK();
+        cm.allreduce_max_u32(ctx, vmax.p, 1);
+        uint32_t hmax = 0;
+        d2h(ctx, &hmax, vmax.p, 1);
+        sync(ctx);
+        if ((uint64_t)hmax * (uint64_t)world < 256) {
+          cm.reduce_scatter_u8(ctx, narrow.p, slice8.p, (size_t)per);
+          widen_u8_to_u32_kernel<<<(unsigned)div_up(per / 4, 256), 256, 0, ctx->stream>>>(reinterpret_cast<const uint32_t *>(slice8.p), per / 4, pcs.gap[id].p);
+          PSC_LAUNCH_CHECK();
+          ctx->launches += 2;
+          as_bytes = true;
+        }
+      }
+      if (!as_bytes) cm.reduce_scatter_u32(ctx, gap_full.p, pcs.gap[id].p, (size_t)per);
       const long cnt = std::max(0L, std::min(per, m + 1 - per * rank));
       pcs.carry[id].alloc(ctx, coarse_carry_tiles(cnt) + 1);
       coarse_carries_u32(ctx, pcs.gap[id].p, cnt, pcs.carry[id].p);

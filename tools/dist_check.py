@@ -22,6 +22,7 @@ D.init(ctx)
 ok = True
 cases = [(name, golden_text(gen, kw, n), sa5, [1000, n // 3 + 7]) for name, gen, kw, n, sa5 in golden_cases()]
 big = textgen.markov(1 << 24, seed=3)
+cases.append(("unary_20000", np.zeros(20000, dtype=np.uint8), None, [5000, 20000 // 3 + 1]))   # gap counters far above one byte
 cases.append(("markov_16Mi", big, None, [1 << 21]))
 for name, text, sa5, mbs in cases:
     n = len(text)
