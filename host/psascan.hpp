@@ -91,6 +91,14 @@ inline void pSAscan_impl(const std::string &input_filename, const std::string &o
   psc_device_info(gpu[0].ctx, gpu_name, sizeof(gpu_name), &free_b, &total_b);
 
   long max_block = psc_max_block_size(gpu[0].ctx, n);
+  // External-memory mode: partial suffix arrays and gap arrays as files in the reference's formats, streaming merge.
+  // Taken when the resident pipeline does not fit the HBM (text + 8 bytes per suffix + the output) or on request.
+  bool em_mode = std::getenv("PSASCAN_EM") != NULL && std::atoi(std::getenv("PSASCAN_EM")) != 0;
+  if (max_block <= 0 && !em_mode) em_mode = psc_max_block_size_files(gpu[0].ctx, n) > 0;
+  if (em_mode) {
+    max_block = psc_max_block_size_files(gpu[0].ctx, n);
+    n_gpus = 1;
+  }
   if (const char *e = std::getenv("PSASCAN_MAX_BLOCK")) max_block = std::max(1L, std::atol(e));
   if (max_block <= 0) {
     std::fprintf(stderr, "\nError: text of %ld bytes does not fit the HBM budget (%.1f GiB free)\n", n,
@@ -116,8 +124,8 @@ inline void pSAscan_impl(const std::string &input_filename, const std::string &o
   std::fprintf(stderr, "GPU = %d x %s, HBM free = %.1fGiB\n", n_gpus, gpu_name, free_b / 1073741824.0);
   std::fprintf(stderr, "Host staging = 2 x %.1fMiB (RAM budget %.1LfMiB), threads = %ld (unused)\n",
                stage / 1048576.0, 1.L * ram_use / (1 << 20), max_threads);
-  std::fprintf(stderr, "Max block size = %ld (%.1LfMiB), blocks = %ld\n\n", max_block,
-               1.L * max_block / (1 << 20), n_blocks);
+  std::fprintf(stderr, "Max block size = %ld (%.1LfMiB), blocks = %ld%s\n\n", max_block,
+               1.L * max_block / (1 << 20), n_blocks, em_mode ? " (external-memory mode: SA parts and gap files on disk)" : "");
 
   for (int g = 1; g < n_gpus; ++g)
     if (psc_init(g, 0, &gpu[g].ctx) != PSC_OK) die_psc("cannot initialise a GPU");
@@ -125,7 +133,7 @@ inline void pSAscan_impl(const std::string &input_filename, const std::string &o
   void *pin = NULL;
   for (int g = 0; g < n_gpus; ++g) {
     if (psc_device_alloc(gpu[g].ctx, (size_t)n, &gpu[g].text_d) != PSC_OK) die_psc("device allocation (text)");
-    if (psc_device_alloc(gpu[g].ctx, 5 * (size_t)cap, &gpu[g].out_d) != PSC_OK) die_psc("device allocation (suffix array)");
+    if (!em_mode && psc_device_alloc(gpu[g].ctx, 5 * (size_t)cap, &gpu[g].out_d) != PSC_OK) die_psc("device allocation (suffix array)");
   }
   if (psc_pinned_alloc(gpu[0].ctx, stage, &pin) != PSC_OK) die_psc("pinned staging buffer");
 
@@ -146,6 +154,30 @@ inline void pSAscan_impl(const std::string &input_filename, const std::string &o
   std::fclose(f);
 
   const double t_sa = wclock();
+  if (em_mode) {
+    // partial suffix arrays next to OUTFILE, gap files next to the -g name (a second disk, src/main.cpp:207), merged
+    // by streaming: psascan_b200/csrc/em.cu.  SA parts of at most ram_use / 20 bytes as in partial_sufsort.hpp:206.
+    const long part_bytes = std::max(4L, ram_use / 20L);
+    int rc = psc_construct_sa_files_d(gpu[0].ctx, (const uint8_t *)gpu[0].text_d, n, max_block, output_filename.c_str(),
+                                      gap_filename.c_str(), part_bytes);
+    if (rc == PSC_ESENTINEL) {
+      std::fprintf(stdout, "\n\nError: byte with value 255 was detected in the input text!\n"
+                           "See the section on limitations in the README for more information.\n");
+      std::fflush(stdout);
+      std::exit(EXIT_FAILURE);
+    }
+    if (rc != PSC_OK) die_psc("suffix array construction (external-memory mode)");
+    const double sa_time = wclock() - t_sa, total_time = wclock() - start;
+    psc_pinned_free(gpu[0].ctx, pin);
+    psc_device_free(gpu[0].ctx, gpu[0].text_d);
+    psc_shutdown(gpu[0].ctx);
+    std::fprintf(stderr, "\n\nComputation finished. Summary:\n");
+    std::fprintf(stderr, "  elapsed time: %.2Lfs (%.4Lfs/MiB)\n", (long double)total_time,
+                 (long double)total_time / ((1.L * n) / (1L << 20)));
+    std::fprintf(stderr, "  speed: %.2LfMiB/s\n", ((1.L * n) / (1L << 20)) / (long double)total_time);
+    std::fprintf(stderr, "  GPU suffix array construction through files: %.3fs (%.1f MB/s)\n", sa_time, n / 1e6 / sa_time);
+    return;
+  }
   if (n_gpus == 1) {
     gpu[0].rc = psc_construct_sa_d(gpu[0].ctx, (const uint8_t *)gpu[0].text_d, n, max_block, (uint8_t *)gpu[0].out_d);
     gpu[0].err = psc_last_error();

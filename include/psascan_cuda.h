@@ -214,6 +214,23 @@ long psc_verify_noalloc_max_n(void);
 int psc_verify_sa_noalloc_d(psc_context *ctx, const uint8_t *text_d, long n, const uint8_t *sa5_d,
                             long violations[4]);
 
+/* ---- external-memory mode: partial suffix arrays and gap arrays as FILES in the reference's
+ * formats, merged by streaming.  text_d[n] resident on the device; per block the SA goes to
+ * `<out_path>.distrfile.<hash>.part<k>` (block-relative int32 items, at most part_bytes per part:
+ * io/distributed_file.hpp:51-125, partial_sufsort.hpp:206-208) and the gap array, v-byte coded on the device, to
+ * `<gap_prefix>.gap.<hash>` (gap_array.hpp:156-182, read by io/async_vbyte_stream_reader.hpp:145-168); the merge
+ * (merge.hpp:54-180) reads every file front to back once and writes the 40-bit suffix array to out_path.  The
+ * temporary files are deleted at the end (merge.hpp:178-179) unless the environment has PSC_KEEP_PARTS.
+ * max_block <= 0: psc_max_block_size_files().  part_bytes <= 0: 1 GiB.  This is where -g / gap_filename of
+ * pSAscan() goes (a second disk for the gap files, src/main.cpp:207). */
+int psc_construct_sa_files_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block, const char *out_path,
+                             const char *gap_prefix, long part_bytes);
+long psc_max_block_size_files(psc_context *ctx, long n);
+/* the v-byte code of the gap files on host buffers (device codec): out must hold 5 * count bytes;
+ * psc_vbyte_decode stores at most cap values and returns the number of complete values in *count */
+int psc_vbyte_encode(psc_context *ctx, const uint32_t *vals, long count, uint8_t *out, long *nbytes);
+int psc_vbyte_decode(psc_context *ctx, const uint8_t *bytes, long nbytes, uint32_t *vals, long cap, long *count);
+
 /* ---- by-products, all on device buffers.
  * psc_delete_sentinel_bytes_d: tools/delete-sentinel-bytes/src/main.cpp:45-104 -- out_d receives the bytes of
  *   in_d[n] that are not 255, in order (out_d must hold n bytes); *n_out = how many.

@@ -184,7 +184,8 @@ struct BlockGate {
   virtual ~BlockGate() {}
 };
 static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
-                                    uint8_t *out_sa5_d, const ChunkSink *sink, const BlockGate *gate);
+                                    uint8_t *out_sa5_d, const ChunkSink *sink, const BlockGate *gate,
+                                    PieceSink *pieces = nullptr);
 // Largest block for a text of n symbols.  io_bytes: text and output buffers the caller has NOT allocated yet
 // (the public query: 6n); the construction entry points size the blocks after their I/O buffers exist,
 // so those are never charged twice.  Nothing is trimmed here: unused cached buffers count as available
@@ -261,8 +262,13 @@ struct HostSink : ChunkSink {
   }
 };
 
+void construct_sa_with_sink(psc_context *ctx, const uint8_t *text_d, long n, long max_block, PieceSink *pieces) {
+  construct_sa_sequential(ctx, text_d, n, max_block, nullptr, nullptr, nullptr, pieces);
+}
+
 static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, long n, long max_block,
-                                    uint8_t *out_sa5_d, const ChunkSink *sink, const BlockGate *gate) {
+                                    uint8_t *out_sa5_d, const ChunkSink *sink, const BlockGate *gate,
+                                    PieceSink *pieces) {
   memset(&ctx->stats, 0, sizeof(ctx->stats));
   ctx->launches = 0;
   if (n == 0) return;
@@ -309,10 +315,21 @@ static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, lon
       gap_of_block(ctx, block_d, m, res.sa.p, res.i0, after_d, t, gt_cur, end, id > 0 ? gt_new : nullptr,
                    gap[id].p);
     }
-    sa[id] = std::move(res.sa);
+    if (pieces) {  // external-memory mode: the block leaves the device now
+      pieces->take(ctx, id, beg, m, res.sa.p, t > 0 ? gap[id].p : nullptr);
+      res.sa.release();
+      gap[id].release();
+    } else {
+      sa[id] = std::move(res.sa);
+    }
     std::swap(gt_cur, gt_new);
   }
   Ga.release(); Gb.release();
+  if (pieces) {
+    sync(ctx);
+    ctx->stats.kernel_launches = ctx->launches;
+    return;
+  }
   if (B == 1) {  // one piece: the block SA goes straight to the 40-bit writer
     if (sink) {
       const long C = merge_chunk_entries();
@@ -401,6 +418,20 @@ int psc_shutdown(psc_context *ctx) {
   cudaStreamDestroy(ctx->side);
   delete ctx;
   return PSC_OK;
+}
+
+/* external-memory mode (em.cu): block SAs and gap arrays go to disk, so only one block's working set, the merge
+ * scratch of one output chunk and the walk's rank stream share the device with the text */
+long psc_max_block_size_files(psc_context *ctx, long n) {
+  if (!ctx || n <= 0) return 0;
+  cudaSetDevice(ctx->device);
+  const double chunk = (double)std::min(n, psc::merge_chunk_entries());
+  double rest = psc::hbm_available(ctx) - 0.3 * (double)n - 32.0 * chunk - 8.0 * (double)std::min(n, 1L << 29);
+  if (rest <= 0) return 0;
+  long mb = (long)(rest / 48.0);
+  mb = std::min(mb, (1L << 31) - 4096);
+  mb = std::min(mb, n);
+  return mb < n ? mb / 32 * 32 : mb;
 }
 
 long psc_max_block_size(psc_context *ctx, long n) {

@@ -49,6 +49,15 @@ struct ChunkSink {
   virtual ~ChunkSink() {}
 };
 
+// takes a finished block out of the pipeline (external-memory mode, em.cu): its SA and gap array are released by
+// the pipeline right after the call
+struct PieceSink {
+  virtual void take(psc_context *ctx, long id, long beg, long m, const uint32_t *sa_d, const uint32_t *gap_d /* null: rightmost block */) = 0;
+  virtual ~PieceSink() {}
+};
+// the block pipeline of api.cu with every block handed to `pieces` instead of being kept for the resident merge
+void construct_sa_with_sink(psc_context *ctx, const uint8_t *text_d, long n, long max_block, PieceSink *pieces);
+
 long merge_chunk_entries();
 void merge_split_slice(psc_context *ctx, const uint32_t *gap_slice_d, long cnt, long u_off, uint64_t e_base,
                        const uint64_t *carry_d, bool last_slice, const uint64_t *q_d, int nq, uint64_t *u_d,

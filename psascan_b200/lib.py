@@ -16,7 +16,8 @@ EXPORTS = [
     "psc_construct_sa_dist_slice_d", "psc_dist_slice_capacity", "psc_verify_sa_d",
     "psc_verify_sa_noalloc_d", "psc_verify_noalloc_max_n", "psc_dist_unique_id", "psc_dist_init",
     "psc_dist_finalize", "psc_dist_stats", "psc_dist_abort", "psc_delete_sentinel_bytes_d",
-    "psc_bwt_from_sa5_d", "psc_isa_samples_d", "psc_verify_sa_slice_d",
+    "psc_bwt_from_sa5_d", "psc_isa_samples_d", "psc_verify_sa_slice_d", "psc_construct_sa_files_d",
+    "psc_max_block_size_files", "psc_vbyte_encode", "psc_vbyte_decode",
 ]
 
 

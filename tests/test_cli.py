@@ -95,3 +95,21 @@ def test_cli_memory_error_text(cli, tmp_path):
     f.write_bytes(b"banana")
     r = run(cli, [str(f), "-m", "5"])
     assert r.returncode == 1 and "Error: not enough memory to run pSAscan." in r.stderr
+
+
+@pytest.mark.gpu
+def test_cli_external_memory_mode(cli, tmp_path):
+    """PSASCAN_EM=1: partial suffix arrays next to OUTFILE, v-byte gap files next to the -g name, streaming
+    merge; the result equals the golden file and no temporary file survives."""
+    gap_dir = tmp_path / "gapdisk"
+    gap_dir.mkdir()
+    for name, gen, kw, n, sa5 in golden_cases()[-3:]:
+        f = tmp_path / (name + ".txt")
+        golden_text(gen, kw, n).tofile(str(f))
+        out = tmp_path / (name + ".sa5")
+        r = run(cli, [str(f), "-o", str(out), "-g", str(gap_dir / name), "-m", "200k"],
+                env={"PSASCAN_EM": "1", "PSASCAN_MAX_BLOCK": str(n // 3 + 1)})
+        assert r.returncode == 0, r.stderr[-2000:]
+        assert "external-memory mode" in r.stderr
+        assert np.array_equal(np.fromfile(str(out), dtype=np.uint8), sa5), name
+        assert sorted(os.listdir(str(gap_dir))) == [] and not [x for x in os.listdir(str(tmp_path)) if "distrfile" in x]
