@@ -226,6 +226,16 @@ int psc_verify_sa_noalloc_d(psc_context *ctx, const uint8_t *text_d, long n, con
 int psc_construct_sa_files_d(psc_context *ctx, const uint8_t *text_d, long n, long max_block, const char *out_path,
                              const char *gap_prefix, long part_bytes);
 long psc_max_block_size_files(psc_context *ctx, long n);
+/* With PSC_KEEP_PARTS the run also leaves every block's gt_begin bits as the reference stores them (reversed, LSB
+ * first, raw bytes: bitvector.hpp:61-79; registered for the reversed index range [n - end, n - beg),
+ * partial_sufsort.hpp:231-234) and `<out_path>.parts.txt` with one line per block:
+ *   beg end sa_base items_per_part n_parts gap_file gt_begin_file
+ * so that any single stage can be re-run on one block from the files (tests/test_em.py does that).
+ * psc_multifile_read_bits: bits [r_lo, r_hi) of a multifile bit sequence (io/multifile.hpp:45-68: file k holds bits
+ * [beg[k], end[k]) from its own bit 0), packed LSB first from bit 0 of out -- the access pattern of
+ * io/multifile_bit_stream_reader.hpp:79-93.  Host only. */
+int psc_multifile_read_bits(int n_files, const long *beg, const long *end, const char *const *names, long r_lo, long r_hi,
+                            uint8_t *out);
 /* the v-byte code of the gap files on host buffers (device codec): out must hold 5 * count bytes;
  * psc_vbyte_decode stores at most cap values and returns the number of complete values in *count */
 int psc_vbyte_encode(psc_context *ctx, const uint32_t *vals, long count, uint8_t *out, long *nbytes);

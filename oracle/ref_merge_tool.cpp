@@ -5,7 +5,7 @@
 // and its merge produce the right suffix array from those files, the formats are the reference's.
 //   ref_merge MANIFEST OUT.sa5
 // MANIFEST (written by the library when PSC_KEEP_PARTS is set): one line per block, left to right:
-//   beg end sa_base items_per_part n_parts gap_file|-
+//   beg end sa_base items_per_part n_parts gap_file|- gt_begin_file|-   (the last field is not used here)
 // The reference's merge deletes every file it has read (merge.hpp:178-179): run it on copies.
 #include <cstdio>
 #include <fstream>

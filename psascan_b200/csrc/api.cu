@@ -316,7 +316,7 @@ static void construct_sa_sequential(psc_context *ctx, const uint8_t *text_d, lon
                    gap[id].p);
     }
     if (pieces) {  // external-memory mode: the block leaves the device now
-      pieces->take(ctx, id, beg, m, res.sa.p, t > 0 ? gap[id].p : nullptr);
+      pieces->take(ctx, id, beg, m, res.sa.p, t > 0 ? gap[id].p : nullptr, id > 0 ? gt_new : nullptr);
       res.sa.release();
       gap[id].release();
     } else {

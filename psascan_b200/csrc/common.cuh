@@ -288,7 +288,8 @@ void gt_begin_from_sa(psc_context *ctx, const uint32_t *sa_d, long m, uint32_t i
 
 // bit-vector layout conversion: forward bits (bit q <-> position lo+q+1) <-> reversed LSB-first
 // bytes with hi = lo + nbits (bit r <-> position hi - r).
-void bits_forward_to_rev(psc_context *ctx, const uint32_t *fwd_d, long nbits, uint8_t *rev_d);
+void bits_forward_to_rev(psc_context *ctx, const uint32_t *fwd_d, long nbits, uint8_t *rev_d,
+                         long fwd_off = 0 /* the range starts at bit fwd_off of fwd_d */);
 void bits_rev_to_forward(psc_context *ctx, const uint8_t *rev_d, long nbits, uint32_t *fwd_d);
 
 }  // namespace psc

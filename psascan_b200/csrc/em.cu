@@ -129,6 +129,7 @@ struct EmBlock {
   long items_per_part = 1;
   int n_parts = 0;
   std::string gap_file;         // empty for the rightmost block
+  std::string gt_file;          // gt_begin bits of the block (PSC_KEEP_PARTS only)
   std::vector<uint64_t> carry;  // sum of the first t * COARSE_TILE counters, t = 0..tiles (gap_array.hpp sums nothing: ours)
   std::vector<uint64_t> voff;   // byte offset of counter t * COARSE_TILE in the gap file
   // cursors of the streaming merge
@@ -175,10 +176,23 @@ struct EmSink : PieceSink {
     }
   }
 
-  void take(psc_context *ctx, long id, long beg, long m, const uint32_t *sa_d, const uint32_t *gap_d) override {
+  void take(psc_context *ctx, long id, long beg, long m, const uint32_t *sa_d, const uint32_t *gap_d,
+            const uint32_t *gt_fwd_d) override {
     EmBlock &b = blocks[id];
     b.beg = beg;
     b.m = m;
+    if (gt_fwd_d && getenv("PSC_KEEP_PARTS")) {
+      // the block's own gt_begin bits as the reference stores them: reversed, LSB first, one file per block
+      // registered for the reversed index range [n - end, n - beg) (partial_sufsort.hpp:231-234, 356-358)
+      const long nbytes = (m + 7) / 8;
+      DevBuf<uint8_t> rev(ctx, nbytes);
+      bits_forward_to_rev(ctx, gt_fwd_d, m, rev.p, beg);
+      b.gt_file = out_path + "." + random_hash();
+      FILE *f = fopen(b.gt_file.c_str(), "w");
+      if (!f) io_fail("cannot create", b.gt_file);
+      write_from_device(ctx, rev.p, (size_t)nbytes, f, b.gt_file);
+      if (fclose(f) != 0) io_fail("close", b.gt_file);
+    }
     // partial suffix array: block-relative int32 items (distributed_file<int>, psascan.hpp:117-120)
     b.sa_base = out_path + ".distrfile." + random_hash();
     b.items_per_part = std::max(1L, part_bytes / 4);
@@ -345,14 +359,14 @@ struct EmSink : PieceSink {
   }
 
   // PSC_KEEP_PARTS: what a reader of the files needs to know (the format test feeds it to the reference's own
-  // merge()): beg end sa_base items_per_part n_parts gap_file
+  // merge()): beg end sa_base items_per_part n_parts gap_file gt_begin_file
   void write_manifest() {
     const std::string name = out_path + ".parts.txt";
     FILE *f = fopen(name.c_str(), "w");
     if (!f) io_fail("cannot create", name);
     for (auto &b : blocks)
-      fprintf(f, "%ld %ld %s %ld %d %s\n", b.beg, b.beg + b.m, b.sa_base.c_str(), b.items_per_part, b.n_parts,
-              b.gap_file.empty() ? "-" : b.gap_file.c_str());
+      fprintf(f, "%ld %ld %s %ld %d %s %s\n", b.beg, b.beg + b.m, b.sa_base.c_str(), b.items_per_part, b.n_parts,
+              b.gap_file.empty() ? "-" : b.gap_file.c_str(), b.gt_file.empty() ? "-" : b.gt_file.c_str());
     fclose(f);
   }
 
@@ -360,6 +374,7 @@ struct EmSink : PieceSink {
     for (auto &b : blocks) {
       for (int k = 0; k < b.n_parts; ++k) unlink((b.sa_base + ".part" + std::to_string(k)).c_str());
       if (!b.gap_file.empty()) unlink(b.gap_file.c_str());
+      if (!b.gt_file.empty()) unlink(b.gt_file.c_str());
     }
   }
 };
@@ -390,6 +405,40 @@ int psc_construct_sa_files_d(psc_context *ctx, const uint8_t *text_d, long n, lo
     if (sink) { if (!getenv("PSC_KEEP_PARTS")) sink->remove_files(); delete sink; }
     return e.code;
   }
+}
+
+/* bits [r_lo, r_hi) of a bit sequence stored as a multifile (io/multifile.hpp:45-68: file k holds bits [beg[k], end[k])
+ * from its own bit 0, LSB first, bitvector.hpp:61-67 / 77-79), packed from bit 0 of out: what
+ * io/multifile_bit_stream_reader.hpp:79-93 hands out bit by bit */
+int psc_multifile_read_bits(int n_files, const long *beg, const long *end, const char *const *names, long r_lo, long r_hi,
+                            uint8_t *out) {
+  if (n_files < 0 || r_lo < 0 || r_hi < r_lo || (r_hi > r_lo && (!beg || !end || !names || !out))) {
+    set_error("psc_multifile_read_bits: bad argument");
+    return PSC_EARG;
+  }
+  memset(out, 0, (size_t)((r_hi - r_lo + 7) / 8));
+  long covered = 0;
+  for (int k = 0; k < n_files; ++k) {
+    const long lo = std::max(r_lo, beg[k]), hi = std::min(r_hi, end[k]);
+    if (hi <= lo) continue;
+    FILE *f = fopen(names[k], "r");
+    if (!f) { set_error("cannot open %s: %s", names[k], strerror(errno)); return PSC_EARG; }
+    const long b0 = (lo - beg[k]) >> 3, b1 = (hi - beg[k] + 7) >> 3;
+    std::vector<uint8_t> raw((size_t)(b1 - b0));
+    if (fseeko(f, (off_t)b0, SEEK_SET) != 0 || fread(raw.data(), 1, raw.size(), f) != raw.size()) {
+      fclose(f);
+      set_error("cannot read %s", names[k]);
+      return PSC_EARG;
+    }
+    fclose(f);
+    for (long r = lo; r < hi; ++r) {
+      const long q = r - beg[k] - (b0 << 3);
+      if ((raw[q >> 3] >> (q & 7)) & 1) out[(r - r_lo) >> 3] |= (uint8_t)(1u << ((r - r_lo) & 7));
+    }
+    covered += hi - lo;
+  }
+  if (covered != r_hi - r_lo) { set_error("psc_multifile_read_bits: the files do not cover [%ld, %ld)", r_lo, r_hi); return PSC_EARG; }
+  return PSC_OK;
 }
 
 int psc_vbyte_encode(psc_context *ctx, const uint32_t *vals, long count, uint8_t *out, long *nbytes) {

@@ -52,7 +52,9 @@ struct ChunkSink {
 // takes a finished block out of the pipeline (external-memory mode, em.cu): its SA and gap array are released by
 // the pipeline right after the call
 struct PieceSink {
-  virtual void take(psc_context *ctx, long id, long beg, long m, const uint32_t *sa_d, const uint32_t *gap_d /* null: rightmost block */) = 0;
+  // gt_fwd_d: the gt bits relative to the block begin, bit j - 1 <-> text position j (null for the leftmost block)
+  virtual void take(psc_context *ctx, long id, long beg, long m, const uint32_t *sa_d, const uint32_t *gap_d /* null: rightmost block */,
+                    const uint32_t *gt_fwd_d) = 0;
   virtual ~PieceSink() {}
 };
 // the block pipeline of api.cu with every block handed to `pieces` instead of being kept for the resident merge

@@ -842,13 +842,13 @@ void gt_begin_from_sa(psc_context *ctx, const uint32_t *sa_d, long m, uint32_t i
 
 // ---- bit-vector layout conversion (bitvector.hpp:61-67, multifile.hpp:57-68) -----------------------
 __global__ void bits_fwd_to_rev_kernel(const uint32_t *__restrict__ fwd, long nbits,
-                                       uint8_t *__restrict__ rev) {
+                                       uint8_t *__restrict__ rev, long fwd_off) {
   long b = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= (nbits + 7) / 8) return;
   uint32_t byte = 0;
   for (int k = 0; k < 8; ++k) {
     long r = b * 8 + k;
-    if (r < nbits && bit_get(fwd, nbits - 1 - r)) byte |= 1u << k;
+    if (r < nbits && bit_get(fwd, fwd_off + nbits - 1 - r)) byte |= 1u << k;
   }
   rev[b] = (uint8_t)byte;
 }
@@ -866,10 +866,10 @@ __global__ void bits_rev_to_fwd_kernel(const uint8_t *__restrict__ rev, long nbi
   }
   fwd[w] = word;
 }
-void bits_forward_to_rev(psc_context *ctx, const uint32_t *fwd_d, long nbits, uint8_t *rev_d) {
+void bits_forward_to_rev(psc_context *ctx, const uint32_t *fwd_d, long nbits, uint8_t *rev_d, long fwd_off) {
   long nb = (nbits + 7) / 8;
   if (!nb) return;
-  bits_fwd_to_rev_kernel<<<(unsigned)div_up(nb, 256), 256, 0, ctx->stream>>>(fwd_d, nbits, rev_d);
+  bits_fwd_to_rev_kernel<<<(unsigned)div_up(nb, 256), 256, 0, ctx->stream>>>(fwd_d, nbits, rev_d, fwd_off);
   PSC_LAUNCH_CHECK();
   ctx->launches++;
 }

@@ -17,7 +17,7 @@ EXPORTS = [
     "psc_verify_sa_noalloc_d", "psc_verify_noalloc_max_n", "psc_dist_unique_id", "psc_dist_init",
     "psc_dist_finalize", "psc_dist_stats", "psc_dist_abort", "psc_delete_sentinel_bytes_d",
     "psc_bwt_from_sa5_d", "psc_isa_samples_d", "psc_verify_sa_slice_d", "psc_construct_sa_files_d",
-    "psc_max_block_size_files", "psc_vbyte_encode", "psc_vbyte_decode",
+    "psc_max_block_size_files", "psc_vbyte_encode", "psc_vbyte_decode", "psc_multifile_read_bits",
 ]
 
 

@@ -94,3 +94,38 @@ def test_reference_merge_reads_our_files(ctx, tmp_path, monkeypatch):
         assert np.array_equal(np.fromfile(out + ".ref", dtype=np.uint8), sa5), (name, "reference merge() on GPU-written files")
         # the reference deleted what it read
         assert not glob.glob(out + ".distrfile.*.part*") and not glob.glob(str(tmp_path / (name + ".g.gap.*")))
+
+
+def test_single_stage_rerun_from_files(ctx, tmp_path, monkeypatch):
+    """with the partial suffix arrays and gt bit files in the reference's layouts on disk, ONE stage can
+    be run again for ONE block from the files alone.  Block sort (psc_sort_block = inmem_psascan()): text range from
+    the text file, tail gt bits through psc_multifile_read_bits from the right neighbour's gt_begin file -- the
+    result must be the block's part files, item for item."""
+    monkeypatch.setenv("PSC_KEEP_PARTS", "1")
+    for name, gen, kw, n, sa5 in golden_cases()[-3:]:
+        text = golden_text(gen, kw, n)
+        mb = (n // 4 + 31) // 32 * 32
+        out = str(tmp_path / (name + ".sa5"))
+        assert np.array_equal(run_files(ctx, text, out, str(tmp_path / (name + ".g")), mb, 6000), sa5)
+        rows = [l.split() for l in open(out + ".parts.txt")]
+        assert len(rows) == -(-n // mb)
+        for k in range(len(rows) - 1):
+            beg, end = int(rows[k][0]), int(rows[k][1])
+            nbeg, nend, ngt = int(rows[k + 1][0]), int(rows[k + 1][1]), rows[k + 1][6]
+            assert nbeg == end and ngt != "-"
+            length = min(end - beg, nend - nbeg)            # tail prefix the sorter looks at (inmem_psascan.hpp:150-156)
+            # positions (end, end + length] relative to `end`, reversed layout with hi = end + length:
+            # global reversed indices [n - (end + length), n - end) of the multifile
+            begs, ends = (C.c_long * 1)(n - nend), (C.c_long * 1)(n - nbeg)
+            names = (C.c_char_p * 1)(ngt.encode())
+            bits = np.zeros((length + 7) // 8, dtype=np.uint8)
+            ctx._chk(ctx.lib.psc_multifile_read_bits(C.c_int(1), begs, ends, names, C.c_long(n - (end + length)), C.c_long(n - end),
+                                                     bits.ctypes.data_as(C.c_void_p)))
+            sa, bwt, gt, i0 = ctx.sort_block(text[beg:end], text[end:end + length], bits)
+            items_per_part, n_parts = int(rows[k][3]), int(rows[k][4])
+            parts = np.concatenate([np.fromfile("%s.part%d" % (rows[k][2], p), dtype=np.int32) for p in range(n_parts)])
+            assert n_parts == -(-(end - beg) // items_per_part)
+            assert np.array_equal(parts.astype(np.int64), sa.astype(np.int64)), (name, k)
+            # and the gt_begin bits this stage returns are the file the run left for this block
+            if rows[k][6] != "-":
+                assert np.array_equal(np.fromfile(rows[k][6], dtype=np.uint8), gt), (name, k, "gt_begin file")
