@@ -83,15 +83,139 @@ void merge_split_next(psc_context *ctx, const uint64_t *q_d, const uint64_t *u_d
   ctx->launches++;
 }
 
-// ---- cascade: one chunk of output slots from its slices ---------------------------------------------
-void MergeScratch::reserve(psc_context *ctx, long entries, bool hi_plane) {
-  if (entries <= cap && hi_plane == has_hi) return;
-  cap = entries;
-  has_hi = hi_plane;
-  for (int k = 0; k < 2; ++k) {
-    lo[k].alloc(ctx, entries);
-    if (hi_plane) hi[k].alloc(ctx, entries); else hi[k].release();
+// ---- one chunk of output slots from its slices ------------------------------------------------------------------
+// Round 2's first version merged level by level into a growing array of (lo, hi) planes: every level rewrote what
+// the levels below had produced, 4.5 x the chunk in total for 8 blocks (36 of 62 ms on the bench workload).  Now a
+// level only contributes a BITMAP over its slots (1 = suffix of this block, at slot u + E'[u+1]) with a popcount
+// directory, and one pass over the output slots walks down the levels: at level k a slot either is the r-th suffix
+// of block k (r = ones before it) or continues as slot (zeros before it) of the level below.  Neighbouring slots
+// take neighbouring paths, so the bitmaps are read through L1/L2; each suffix array entry is read once and each
+// 40-bit value written once.
+struct DescentLevel {
+  const uint2 *bd;   // per 32 slots: x = bitmap word, y = ones before the word (counted over the bitmaps of ALL levels
+                     // of the chunk); nullptr: bottom level, every slot is a suffix of this block
+  uint32_t rebase;   // ones of the levels above (their suffixes), subtracted from y
+  const uint32_t *sa;
+  uint64_t beg;
+};
+constexpr int DESCENT_MAX_LEVELS = 64;  // per kernel launch; more blocks than that go through device memory
+struct DescentLevels { DescentLevel lv[DESCENT_MAX_LEVELS]; int n; };
+
+// Bits of one level from its gap slice, fused with the scan: tile t (SCAN tile of 2048 counters) knows the sum of
+// the counters before it (agg, scanned), every thread the inclusive sums of its 8 counters, hence the slot
+// u + E'[u+1] of every suffix u.  Slots grow with u, so the slots of a tile form a range no other tile writes
+// into except for its first and last word: the range is built in shared memory and stored, the two boundary words
+// (and ranges too long for shared memory) go through atomicOr.
+constexpr int LB_ITEMS = 8, LB_TILE = SC_THREADS * LB_ITEMS, LB_WORDS = 1024;  // 64 Ki slots per tile in shared memory
+static_assert(LB_TILE == COARSE_TILE, "tiles of the level-bits kernel are the scan's tiles");
+
+__global__ void __launch_bounds__(SC_THREADS)
+    level_bits_kernel(const uint32_t *__restrict__ gap, long cb, const uint64_t *__restrict__ agg /* scanned tile sums */,
+                      uint64_t skip, unsigned long long *__restrict__ bits) {
+  __shared__ uint64_t sm[SC_THREADS / 32 + 1];
+  __shared__ unsigned long long shw[LB_WORDS];
+  __shared__ uint64_t range[2];
+  const long base = (long)blockIdx.x * LB_TILE + (long)threadIdx.x * LB_ITEMS;
+  uint32_t v[LB_ITEMS];
+  uint64_t s = 0;
+#pragma unroll
+  for (int k = 0; k < LB_ITEMS; ++k) { v[k] = base + k < cb ? gap[base + k] : 0u; s += v[k]; }
+  uint64_t tot;
+  uint64_t incl = block_excl_sum<uint64_t>(s, sm, &tot) + agg[blockIdx.x] - skip;  // E'[base] (skip leaves after entry 0)
+  // slot of suffix u = u + E'[u + 1] = u + (sum of counters 0..u) - skip
+  const long tile_first = (long)blockIdx.x * LB_TILE, tile_last = min(cb, tile_first + LB_TILE) - 1;
+  if (threadIdx.x == 0) range[0] = ~0ull;
+  __syncthreads();
+  uint64_t slot[LB_ITEMS];
+#pragma unroll
+  for (int k = 0; k < LB_ITEMS; ++k) {
+    incl += v[k];
+    slot[k] = (uint64_t)(base + k) + incl;
+    if (base + k == tile_first) range[0] = slot[k];
+    if (base + k == tile_last) range[1] = slot[k];
   }
+  __syncthreads();
+  const uint64_t w0 = range[0] >> 6, w1 = range[1] >> 6;
+  if (w1 - w0 + 1 > (uint64_t)LB_WORDS) {  // a very sparse stretch: straight to global memory
+#pragma unroll
+    for (int k = 0; k < LB_ITEMS; ++k)
+      if (base + k < cb) atomicOr(&bits[slot[k] >> 6], 1ull << (slot[k] & 63));
+    return;
+  }
+  const int nwords = (int)(w1 - w0 + 1);
+  for (int w = threadIdx.x; w < nwords; w += SC_THREADS) shw[w] = 0ull;
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < LB_ITEMS; ++k)
+    if (base + k < cb) atomicOr(&shw[(slot[k] >> 6) - w0], 1ull << (slot[k] & 63));
+  __syncthreads();
+  for (int w = threadIdx.x; w < nwords; w += SC_THREADS) {
+    if (w == 0 || w == nwords - 1) { if (shw[w]) atomicOr(&bits[w0 + w], shw[w]); }
+    else bits[w0 + w] = shw[w];
+  }
+}
+
+// {word, ones before it} side by side: one 8-byte load per level and slot.  Positions inside a chunk fit 32 bits
+// (chunks have at most 2^27 slots), which keeps the walk at about ten instructions per level: the pass is bound
+// by instruction issue, not by memory (64-bit words and directories measured 25 ms per 2^31 slots).
+__global__ void __launch_bounds__(256)
+    word_popc_kernel(const uint32_t *__restrict__ bits, long nwords, uint32_t *__restrict__ cnt) {
+  const long w = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w < nwords) cnt[w] = (uint32_t)__popc(bits[w]);
+}
+__global__ void __launch_bounds__(256)
+    interleave_kernel(const uint32_t *__restrict__ bits, const uint64_t *__restrict__ dir, long nwords,
+                      uint2 *__restrict__ bd) {
+  const long w = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w < nwords) bd[w] = make_uint2(bits[w], (uint32_t)dir[w]);
+}
+
+__device__ __forceinline__ uint64_t descend(const DescentLevel *__restrict__ lv, int n, uint32_t pos) {
+  for (int k = 0; k < n; ++k) {
+    const uint2 *bd = lv[k].bd;
+    if (!bd) return lv[k].beg + lv[k].sa[pos];
+    const uint2 e = bd[pos >> 5];
+    const uint32_t b = pos & 31u;
+    const uint32_t ones = e.y - lv[k].rebase + (uint32_t)__popc(e.x & ((1u << b) - 1u));
+    if ((e.x >> b) & 1u) return lv[k].beg + lv[k].sa[ones];
+    pos -= ones;
+  }
+  return 0;  // not reached: the last level has no bitmap
+}
+
+// 4 slots = 20 bytes = 5 aligned words per thread
+__global__ void __launch_bounds__(256)
+    descent_kernel(const __grid_constant__ DescentLevels dl, const DescentLevel *__restrict__ lv_d, long total,
+                   uint32_t *out_words, uint8_t *out_bytes) {
+  const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long i = g * 4;
+  if (i >= total) return;
+  const DescentLevel *lv = lv_d ? lv_d : dl.lv;
+  if (i + 4 <= total) {
+    uint64_t v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = descend(lv, dl.n, (uint32_t)(i + j));
+    const uint32_t l0 = (uint32_t)v[0], l1 = (uint32_t)v[1], l2 = (uint32_t)v[2], l3 = (uint32_t)v[3];
+    const uint32_t h0 = (uint32_t)(v[0] >> 32) & 255, h1 = (uint32_t)(v[1] >> 32) & 255, h2 = (uint32_t)(v[2] >> 32) & 255,
+                   h3 = (uint32_t)(v[3] >> 32) & 255;
+    uint32_t *o = out_words + g * 5;
+    o[0] = l0;
+    o[1] = h0 | (l1 << 8);
+    o[2] = (l1 >> 24) | (h1 << 8) | (l2 << 16);
+    o[3] = (l2 >> 16) | (h2 << 16) | (l3 << 24);
+    o[4] = (l3 >> 8) | (h3 << 24);
+  } else {
+    for (long k = i; k < total; ++k) {
+      const uint64_t v = descend(lv, dl.n, (uint32_t)k);
+      uint8_t *o = out_bytes + k * 5;
+      for (int b = 0; b < 5; ++b) o[b] = (uint8_t)(v >> (8 * b));
+    }
+  }
+}
+
+void MergeScratch::reserve(psc_context *ctx, long entries, bool) {
+  if (entries <= cap) return;
+  cap = entries;
   E.alloc(ctx, entries + 2);
 }
 
@@ -99,25 +223,76 @@ void cascade_chunk(psc_context *ctx, const LevelSlice *lv, int n_levels, long to
                    uint8_t *out5_d) {
   if (total <= 0) return;
   if (total > scr.cap) { set_error("cascade_chunk: chunk of %ld entries exceeds the scratch (%ld)", total, scr.cap); throw CudaError{PSC_EARG}; }
-  int cur = -1;
-  long have = 0;  // entries merged so far: the chunk's share of the levels below
-  for (int k = n_levels - 1; k >= 0; --k) {
-    const long cb = lv[k].cb;
-    if (cb == 0) continue;  // no suffix of this block in the chunk: the level is the identity
-    const int nxt = cur < 0 ? 0 : 1 - cur;
-    if (have == 0) {
-      sa_slice_to_planes(ctx, lv[k].sa, cb, lv[k].beg, scr.lo[nxt].p, scr.hi[nxt].p);
-    } else {
-      // chunk-local scan: the first `skip` right-side entries of the first run belong to the chunk before
-      exclusive_scan_u32_to_u64(ctx, lv[k].gap, scr.E.p, cb + 1, nullptr, lv[k].skip);
-      merge_level_range(ctx, lv[k].sa, scr.E.p, cb, lv[k].beg, scr.lo[cur].p, scr.hi[cur].p, 0, 0, have + cb,
-                        scr.lo[nxt].p, scr.hi[nxt].p);
-    }
-    cur = nxt;
-    have += cb;
-  }
+  // levels that hold suffixes of the chunk, left to right; L = slots of the level inside the chunk
+  std::vector<int> live;
+  long have = 0;
+  for (int k = 0; k < n_levels; ++k) if (lv[k].cb > 0) { live.push_back(k); have += lv[k].cb; }
   if (have != total) { set_error("cascade_chunk: slices hold %ld entries, the chunk has %ld slots", have, total); throw CudaError{PSC_EARG}; }
-  pack_sa5(ctx, scr.lo[cur].p, scr.hi[cur].p, total, out5_d);
+  const int nl = (int)live.size();
+  std::vector<DescentLevel> host(nl);
+  // one allocation for all bitmaps and directories: words of level j = L_j / 64 + 1
+  std::vector<long> L(nl), woff(nl + 1, 0);
+  {
+    long slots = total;
+    for (int j = 0; j < nl; ++j) { L[j] = slots; woff[j + 1] = woff[j] + (j + 1 < nl ? slots / 64 + 1 : 0); slots -= lv[live[j]].cb; }
+  }
+  const long words = std::max(1L, woff[nl]);
+  // `words` 64-bit words are built (level_bits_kernel), read as 2 * words 32-bit words afterwards
+  const long w32 = 2 * words;
+  DevBuf<uint64_t> bits(ctx, words), dir(ctx, w32);
+  DevBuf<uint2> bd(ctx, w32);
+  DevBuf<uint32_t> cnt(ctx, w32);
+  PSC_CUDA(cudaMemsetAsync(bits.p, 0, (size_t)words * 8, ctx->stream));
+  for (int j = 0; j < nl; ++j) {
+    const LevelSlice &s = lv[live[j]];
+    host[j].sa = s.sa;
+    host[j].beg = (uint64_t)s.beg;
+    host[j].bd = nullptr;
+    host[j].rebase = 0;
+    if (j + 1 == nl) break;  // bottom level
+    // tile sums of the gap slice, scanned; then the bits of every tile (the scanned counters themselves are never stored)
+    KTrace kt(ctx, "merge_bits");
+    const long tiles = coarse_carry_tiles(s.cb);
+    coarse_carries_u32(ctx, s.gap, s.cb, scr.E.p);  // E[t] = sum of the counters before tile t
+    level_bits_kernel<<<(unsigned)tiles, SC_THREADS, 0, ctx->stream>>>(s.gap, s.cb, scr.E.p, s.skip,
+                                                                        reinterpret_cast<unsigned long long *>(bits.p + woff[j]));
+    PSC_LAUNCH_CHECK();
+    ctx->launches++;
+    host[j].bd = bd.p + 2 * woff[j];
+  }
+  if (woff[nl] > 0) {  // directories of all levels at once: per-word popcounts, one scan, interleaved with the words
+    KTrace kt(ctx, "merge_dir");
+    const uint32_t *b32 = reinterpret_cast<const uint32_t *>(bits.p);
+    word_popc_kernel<<<(unsigned)div_up(w32, 256), 256, 0, ctx->stream>>>(b32, w32, cnt.p);
+    PSC_LAUNCH_CHECK();
+    exclusive_scan_u32_to_u64(ctx, cnt.p, dir.p, w32, nullptr);
+    interleave_kernel<<<(unsigned)div_up(w32, 256), 256, 0, ctx->stream>>>(b32, dir.p, w32, bd.p);
+    PSC_LAUNCH_CHECK();
+    ctx->launches += 2;
+  }
+  // the scan runs over all levels: level j's directory is offset by the ones of the levels before it, which is the
+  // number of suffixes of those levels -- known on the host
+  DescentLevels dl;
+  memset(&dl, 0, sizeof(dl));
+  dl.n = nl;
+  DevBuf<DescentLevel> lv_d;
+  uint64_t ones_before = 0;
+  for (int j = 0; j < nl; ++j) {
+    if (host[j].bd) host[j].rebase = (uint32_t)ones_before;
+    ones_before += (uint64_t)lv[live[j]].cb;
+  }
+  if (nl <= DESCENT_MAX_LEVELS) {
+    for (int j = 0; j < nl; ++j) dl.lv[j] = host[j];
+  } else {
+    lv_d.alloc(ctx, nl);
+    h2d(ctx, lv_d.p, host.data(), (size_t)nl);
+    sync(ctx);
+  }
+  KTrace kt(ctx, "merge_descent");
+  descent_kernel<<<(unsigned)div_up(div_up(total, 4), 256), 256, 0, ctx->stream>>>(dl, lv_d.p, total,
+                                                                                     reinterpret_cast<uint32_t *>(out5_d), out5_d);
+  PSC_LAUNCH_CHECK();
+  ctx->launches++;
 }
 
 // ---- one GPU, everything resident -------------------------------------------------------------------

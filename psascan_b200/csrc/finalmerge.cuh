@@ -22,12 +22,9 @@ struct LevelSlice {
 };
 
 struct MergeScratch {
-  DevBuf<uint32_t> lo[2];
-  DevBuf<uint8_t> hi[2];
-  DevBuf<uint64_t> E;
+  DevBuf<uint64_t> E;  // scanned gap slice of one level
   long cap = 0;
-  bool has_hi = false;
-  void reserve(psc_context *ctx, long entries, bool hi_plane);
+  void reserve(psc_context *ctx, long entries, bool hi_plane /* unused: values are 40 bits wide on the way out */);
 };
 
 // host copy of the split tables: for level k and boundary i, Q = slot in M_k, U = block-k suffixes below
