@@ -395,7 +395,11 @@ int psc_init(int device, size_t hbm_budget, psc_context **out) {
     cudaDeviceProp prop;
     PSC_CUDA(cudaGetDeviceProperties(&prop, device));
     c->n_sm = prop.multiProcessorCount;
-    PSC_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    // the pipeline's stream gets the highest priority: the block scheduler then places its CTAs before those of
+    // work that only accompanies it (copies on the side stream, the multi-GPU helper's stream, dist.cu)
+    int prio_least = 0, prio_greatest = 0;
+    PSC_CUDA(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
+    PSC_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_greatest));
     PSC_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
     PSC_CUDA(cudaDeviceGetDefaultMemPool(&c->pool, device));
     uint64_t thr = UINT64_MAX;
@@ -410,6 +414,7 @@ int psc_init(int device, size_t hbm_budget, psc_context **out) {
 int psc_shutdown(psc_context *ctx) {
   if (!ctx) return PSC_OK;
   cudaSetDevice(ctx->device);
+  psc_dist_finalize(ctx);  // no-op unless psc_dist_init was called and not undone
   hash_domain_clear(ctx);
   cache_trim(ctx);
   cudaStreamSynchronize(ctx->stream);

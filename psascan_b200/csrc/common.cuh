@@ -41,6 +41,8 @@ struct psc_context {
   int device = 0;
   psc::TextHashStore *thash = nullptr;  // texthash.cu: fingerprints of the text of the running construction
   psc::Comm *comm = nullptr;  // psc_dist_init (comm.cu): this context is one rank of a multi-GPU construction
+  psc_context *helper = nullptr;  // psc_dist_init: second stream + buffer cache for the thread that prepares the
+                                  // next blocks during a walk (dist.cu, BlockFeeder)
   int n_sm = 148;
   size_t hbm_budget = 0;
   cudaStream_t stream = nullptr;

@@ -3,11 +3,12 @@
 //   phase 1  block sorts are independent once gt_end is computed by plain text comparison past the
 //            block end (no gt bits of the next block needed): rank r sorts blocks B-1-r, B-1-r-N, ...
 //            and keeps their SA; BWT, gt_begin bits and i0 wait for phase 2.
-//   phase 2  blocks right to left.  The owner computes the start ranks of ALL ranks' walkers (K5 needs
-//            the block SA, which never leaves its owner) and broadcasts [start ranks | gt_begin bits |
-//            BWT]: m bytes + a few MB instead of the 5m of round 1.  Every rank builds the rank
-//            structure, walks ITS share of the tail (compute_gap.hpp:68-69 cuts the tail over threads
-//            the same way; shares begin on 32-bit word boundaries of the gt bit array), then
+//   phase 2  blocks right to left.  The owner broadcasts [gt_begin bits | BWT] (m bytes + m/8 instead of
+//            the 5m of round 1) and every rank builds the rank structure.  The owner then computes the
+//            start ranks of ALL ranks' walkers (K5 needs the block SA, which never leaves its owner, and
+//            the gt bits the previous walk produced) and broadcasts them (a few MB).  Every rank walks ITS
+//            share of the tail (compute_gap.hpp:68-69 cuts the tail over threads the same way; shares
+//            begin on 32-bit word boundaries of the gt bit array), then
 //              ncclReduceScatter(sum, uint32) of the gap counts: every rank keeps a 1/N slice per block,
 //              ncclAllGather of the new gt words (disjoint word ranges, no reduction).
 //   phase 3  the N-way merge by output range (finalmerge.cu): rank g produces output slots
@@ -18,9 +19,15 @@
 //            except the text.
 // All collectives are enqueued on the context's stream (comm.cu); the host only waits where it needs
 // a value (block meta data, split tables).
+// PSC_DIST_HELPER=1 (experimental, off by default) moves the package broadcast + rank build of the next block
+// and the reduce-scatter of the previous one to a helper thread with its own stream (BlockFeeder below).
 #include <algorithm>
+#include <condition_variable>
+#include <functional>
 #include <memory>
+#include <mutex>
 #include <string>
+#include <thread>
 #include "comm.cuh"
 #include "finalmerge.cuh"
 #include "texthash.cuh"
@@ -66,17 +73,24 @@ __global__ void __launch_bounds__(256)
   reinterpret_cast<uint4 *>(out)[i] = make_uint4(v & 255u, (v >> 8) & 255u, (v >> 16) & 255u, v >> 24);
 }
 
-struct OwnedBlock {
-  DevBuf<uint32_t> sa;
-  DevBuf<uint8_t> bwt;
-  DevBuf<uint32_t> gtb;  // bit q <-> block position q+1, q in [0, m-1)
-  long i0 = 0;
-  int end_bit = 0;       // gt bit of position `end` relative to the block begin
-  uint8_t last = 0;      // text[end - 1]
-};
-
 struct BlockMeta { long long i0; int end_bit; int last; };
 constexpr size_t META_BYTES = 256;
+
+// what a block's owner sends to everybody, one contiguous package: [meta | gt_begin bits | BWT]
+struct PackLayout {
+  size_t gtb_off = META_BYTES, gtb_bytes = 0, bwt_off = 0, total = 0;
+  PackLayout(long m, bool has_tail) {
+    gtb_bytes = (size_t)(m / 32 + 2) * 4;
+    bwt_off = gtb_off + ((gtb_bytes + 255) & ~(size_t)255);
+    total = bwt_off + (has_tail ? (size_t)m : 0);
+  }
+};
+
+struct OwnedBlock {
+  DevBuf<uint32_t> sa;
+  DevBuf<uint8_t> pack;  // PackLayout: gt bit q <-> block position q+1, q in [0, m-1); BWT only if the block has a tail
+  BlockMeta meta{0, 0, 0};  // i0, gt bit of position `end` relative to the block begin, text[end - 1]
+};
 
 // K0 (by plain comparison past the block end) + block sort + gt_begin bits + BWT of text[beg, end):
 // everything a block contributes that does not depend on the blocks to its right.
@@ -92,18 +106,19 @@ static std::unique_ptr<OwnedBlock> sort_owned_block(psc_context *ctx, const uint
   }
   sort_block(ctx, text_d + beg, m, t > 0 ? gt_end.p : nullptr, &res);
   res.isa.release();
-  ob->i0 = res.i0;
-  ob->gtb.alloc(ctx, m / 32 + 2);
-  ob->gtb.zero();
-  gt_begin_from_sa(ctx, res.sa.p, m, (uint32_t)res.i0, ob->gtb.p, 0);
+  const PackLayout lay(m, t > 0);
+  ob->pack.alloc(ctx, lay.total);
+  uint32_t *gtb = reinterpret_cast<uint32_t *>(ob->pack.p + lay.gtb_off);
+  PSC_CUDA(cudaMemsetAsync(ob->pack.p, 0, lay.bwt_off, ctx->stream));
+  gt_begin_from_sa(ctx, res.sa.p, m, (uint32_t)res.i0, gtb, 0);
   uint32_t w0 = 1;  // gt_end[0]: 1 for the last block
   if (t > 0) { d2h(ctx, &w0, gt_end.p, 1); sync(ctx); }
-  ob->end_bit = (w0 & 1u) ? 0 : 1;  // !gt_end[beg]  (change_gt_reference_point.hpp)
-  if (t > 0) {
-    ob->bwt.alloc(ctx, m);
-    bwt_from_sa(ctx, text_d + beg, res.sa.p, m, ob->bwt.p);
-  }
-  PSC_CUDA(cudaMemcpyAsync(&ob->last, text_d + end - 1, 1, cudaMemcpyDeviceToHost, ctx->stream));
+  if (t > 0) bwt_from_sa(ctx, text_d + beg, res.sa.p, m, ob->pack.p + lay.bwt_off);
+  uint8_t last = 0;
+  PSC_CUDA(cudaMemcpyAsync(&last, text_d + end - 1, 1, cudaMemcpyDeviceToHost, ctx->stream));
+  sync(ctx);
+  ob->meta = BlockMeta{(long long)res.i0, (w0 & 1u) ? 0 : 1 /* !gt_end[beg], change_gt_reference_point.hpp */, (int)last};
+  h2d(ctx, reinterpret_cast<BlockMeta *>(ob->pack.p), &ob->meta, 1);
   ob->sa = std::move(res.sa);
   sync(ctx);
   return ob;
@@ -148,6 +163,192 @@ struct DistPieces {  // what a rank keeps of every block until the final merge
   std::vector<long> per;                  // slice length (entries per rank) of every block
 };
 
+// PSC_TRACE: host time spent waiting (for the helper thread), in the same table as the kernel times
+struct HostTrace {
+  psc_context *ctx;
+  const char *name;
+  std::chrono::steady_clock::time_point t0;
+  HostTrace(psc_context *c, const char *n) : ctx(c), name(n), t0(std::chrono::steady_clock::now()) {}
+  ~HostTrace() {
+    if (!ctx->trace) return;
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    for (auto &r : ctx->trace_rows)
+      if (r.name == name) { r.count++; r.ms += ms; return; }
+    ctx->trace_rows.push_back({name, 1, ms});
+  }
+};
+
+// What a rank needs of a block before it can walk the block's tail: the owner's package and the rank structure
+// built from its BWT.
+struct BlockFeed {
+  DevBuf<uint8_t> recv;          // ranks that do not own the block: the received package
+  const uint8_t *pack = nullptr;  // the package (the owner's own copy, or `recv`)
+  BlockMeta meta{0, 0, 0};
+  psc_rank *rk = nullptr;
+  void clear() { rank_free(rk); rk = nullptr; recv.release(); pack = nullptr; }
+};
+
+// The helper thread of a rank: it works on its own context (stream + buffer cache), so what it enqueues runs on
+// the device beside the walk the main thread is busy with:
+//   pre(k)   the feed of the k-th block (block B-1 is the 0-th): broadcast of the owner's package + rank structure;
+//   post(k)  the job the main thread hands over after the walk of the k-th block: summing the gap counters over
+//            the ranks, which nothing needs before the final merge.
+// Both threads use ONE communicator, and NCCL wants every rank to issue its collectives in the same order, so
+// the right to issue them is a token that moves through a fixed sequence of turns:
+//   helper: pre(0) pre(1) | for k = 0 .. B-1:  main: start ranks of k | helper: post(k-1) pre(k+1) | main: gt words
+//   of k (after the walk) | and last helper: post(B-1).
+// The helper's turn of step k falls into the walk of block k, which is where its device work hides; a feed
+// occupies one of two slots until the main thread is done with it.  Waits only ever point to earlier turns.
+// Without a helper context everything happens in place on the caller's thread.
+class BlockFeeder {
+ public:
+  using Job = std::function<void(psc_context *, Comm &)>;
+  BlockFeeder(psc_context *ctx, Comm &cm, psc_context *hctx, long n, long max_block, long B,
+              std::vector<std::unique_ptr<OwnedBlock>> &mine)
+      : ctx_(ctx), cm_(cm), hctx_(hctx), n_(n), max_block_(max_block), B_(B), mine_(mine) {
+    if (hctx_) {
+      memset(&hctx_->stats, 0, sizeof(hctx_->stats));
+      hctx_->launches = 0;
+      th_ = std::thread([this] { run(); });
+    }
+  }
+  ~BlockFeeder() {
+    if (th_.joinable()) {
+      { std::lock_guard<std::mutex> lk(mu_); stop_ = true; }
+      cv_.notify_all();
+      th_.join();
+      collect();
+    }
+    // the caller has synchronised its stream after the last use of a feed (done()), or is unwinding
+    cudaStreamSynchronize(ctx_->stream);
+    for (auto &sl : slot_) sl.feed.clear();
+  }
+  // turns of the main thread in step k (k-th block from the right): 0 = start ranks, 1 = gt words
+  void acquire(long k, int which) { wait_turn(1 + 3 * k + (which ? 2 : 0), false); }
+  void release() { pass(); }
+  BlockFeed *get(long id) {
+    Slot &sl = slot_[(B_ - 1 - id) & 1];
+    if (!th_.joinable()) {
+      produce(ctx_, id, sl.feed);
+      return &sl.feed;
+    }
+    std::unique_lock<std::mutex> lk(mu_);
+    cv_.wait(lk, [&] { return failed_ || (sl.ready && sl.id == id); });
+    rethrow();
+    return &sl.feed;
+  }
+  // the caller's stream has finished with block id's feed; `job` (may be empty) is what is left to do for the block
+  void done(long id, Job job) {
+    Slot &sl = slot_[(B_ - 1 - id) & 1];
+    sl.feed.clear();
+    static const bool defer = !getenv("PSC_DIST_DEFER") || atoi(getenv("PSC_DIST_DEFER")) != 0;
+    if (!th_.joinable() || !defer) {  // the caller holds the turn
+      if (job) job(ctx_, cm_);
+      if (!th_.joinable()) return;
+      job = nullptr;
+    }
+    std::lock_guard<std::mutex> lk(mu_);
+    sl.job = std::move(job);
+    sl.ready = false;
+    sl.id = -1;
+  }
+  // all jobs have run and their results are complete in device memory
+  void finish() {
+    if (!th_.joinable()) return;
+    th_.join();
+    collect();
+    rethrow();
+  }
+
+ private:
+  struct Slot { BlockFeed feed; long id = -1; bool ready = false; Job job; };
+  void rethrow() {
+    if (failed_) { set_error("%s", err_.c_str()); throw CudaError{err_code_}; }
+  }
+  // false: stopped (helper only)
+  bool wait_turn(long pos, bool helper) {
+    if (!th_.joinable() && !helper) return true;
+    std::unique_lock<std::mutex> lk(mu_);
+    cv_.wait(lk, [&] { return failed_ || (helper && stop_) || turn_ == pos; });
+    if (!helper) rethrow();
+    return turn_ == pos && !failed_;
+  }
+  void pass() {
+    if (!th_.joinable()) return;
+    { std::lock_guard<std::mutex> lk(mu_); ++turn_; }
+    cv_.notify_all();
+  }
+  void collect() {
+    ctx_->stats.ms_rank_build += hctx_->stats.ms_rank_build;
+    ctx_->launches += hctx_->launches;
+    hctx_->launches = 0;
+    hctx_->stats.ms_rank_build = 0;
+  }
+  void produce(psc_context *c, long id, BlockFeed &f) {
+    const long beg = id * max_block_, end = std::min(n_, beg + max_block_), m = end - beg, t = n_ - end;
+    const int own = (int)((B_ - 1 - id) % cm_.world);
+    const PackLayout lay(m, t > 0);
+    uint8_t *p;
+    if (own == cm_.rank) {
+      p = mine_[id]->pack.p;
+      f.meta = mine_[id]->meta;
+    } else {
+      f.recv.alloc(c, lay.total);
+      p = f.recv.p;
+    }
+    cm_.bcast(c, p, lay.total, own);
+    if (own != cm_.rank) { d2h(c, &f.meta, reinterpret_cast<const BlockMeta *>(p), 1); sync(c); }
+    f.pack = p;
+    if (t > 0) f.rk = rank_build(c, p + lay.bwt_off, m, (long)f.meta.i0);
+    sync(c);
+  }
+  void publish(long k) {
+    { std::lock_guard<std::mutex> lk(mu_); slot_[k & 1].id = B_ - 1 - k; slot_[k & 1].ready = true; }
+    cv_.notify_all();
+  }
+  void run_job(long k) {  // handed over by done() before the main thread passed the turn
+    Job job;
+    { std::lock_guard<std::mutex> lk(mu_); job = std::move(slot_[k & 1].job); slot_[k & 1].job = nullptr; }
+    if (job) { job(hctx_, cm_); sync(hctx_); }
+  }
+  void run() {
+    try {
+      PSC_CUDA(cudaSetDevice(hctx_->device));
+      for (long k = 0; k < 2 && k < B_; ++k) { produce(hctx_, B_ - 1 - k, slot_[k & 1].feed); publish(k); }
+      pass();
+      for (long k = 0; k < B_; ++k) {
+        if (!wait_turn(2 + 3 * k, true)) return;
+        if (k >= 1) {
+          run_job(k - 1);
+          if (k + 1 < B_) { produce(hctx_, B_ - 1 - (k + 1), slot_[(k + 1) & 1].feed); publish(k + 1); }
+        }
+        pass();
+      }
+      if (!wait_turn(1 + 3 * B_, true)) return;
+      run_job(B_ - 1);
+    } catch (const CudaError &e) {
+      std::lock_guard<std::mutex> lk(mu_);
+      failed_ = true;
+      err_code_ = e.code;
+      err_ = psc_last_error();  // the message is thread-local: hand it to the consumer
+      cv_.notify_all();
+    }
+  }
+  psc_context *ctx_;
+  Comm &cm_;
+  psc_context *hctx_;
+  long n_, max_block_, B_;
+  std::vector<std::unique_ptr<OwnedBlock>> &mine_;
+  Slot slot_[2];
+  std::thread th_;
+  std::mutex mu_;
+  std::condition_variable cv_;
+  long turn_ = 0;
+  bool stop_ = false, failed_ = false;
+  int err_code_ = PSC_ECUDA;
+  std::string err_;
+};
+
 // phases 1 and 2; fills `pcs`, totals_d[g * B + id] = sum of rank g's gap slice of block id
 static void dist_blocks(psc_context *ctx, Comm &cm, const uint8_t *text_d, long n, long max_block, long B,
                         DistPieces &pcs, DevBuf<uint64_t> &totals_d) {
@@ -174,6 +375,8 @@ static void dist_blocks(psc_context *ctx, Comm &cm, const uint8_t *text_d, long 
   totals_d.zero();
   DevBuf<uint64_t> my_tot(ctx, B);
   my_tot.zero();
+  sync(ctx);  // the helper thread reads what phase 1 wrote
+  BlockFeeder feeder(ctx, cm, ctx->helper, n, max_block, B, mine);
   for (long id = B - 1; id >= 0; --id) {
     long beg, end;
     bounds(id, &beg, &end);
@@ -192,85 +395,85 @@ static void dist_blocks(psc_context *ctx, Comm &cm, const uint8_t *text_d, long 
       }
     }
     const long nbnd = off[world];
-    // one broadcast per block: [meta | walker boundaries' ranks | gt_begin bits | BWT]
-    const size_t sr_off = META_BYTES, sr_bytes = ((size_t)nbnd * 8 + 255) & ~(size_t)255;
-    const size_t gtb_off = sr_off + sr_bytes, gtb_bytes = (size_t)(m / 32 + 2) * 4;
-    const size_t bwt_off = gtb_off + ((gtb_bytes + 255) & ~(size_t)255);
-    const size_t total = bwt_off + (t > 0 ? (size_t)m : 0);
-    DevBuf<uint8_t> pack(ctx, total);
-    uint64_t *sr_p = reinterpret_cast<uint64_t *>(pack.p + sr_off);
-    uint32_t *gtb_p = reinterpret_cast<uint32_t *>(pack.p + gtb_off);
-    uint8_t *bwt_p = t > 0 ? pack.p + bwt_off : nullptr;
-    DevBuf<uint64_t> b_d(ctx, std::max(1L, nbnd));
+    DevBuf<uint64_t> b_d(ctx, std::max(1L, nbnd)), sr(ctx, std::max(1L, nbnd));
+    const long step = B - 1 - id;
+    { HostTrace ht(ctx, "dist_turn_wait(host)"); feeder.acquire(step, 0); }
     if (nbnd > 0) {
       std::vector<uint64_t> all_b((size_t)nbnd);
       for (int g = 0; g < world; ++g) std::copy(plans[g].b.begin(), plans[g].b.end(), all_b.begin() + off[g]);
       h2d(ctx, b_d.p, all_b.data(), all_b.size());
       sync(ctx);  // all_b is a local vector
+      // K5 for everybody's walkers: the rank of suffix(end + b) among the block's suffixes, from the owner
+      KTrace kt(ctx, "dist_start_ranks");
+      if (own == rank)
+        initial_ranks(ctx, text_d + beg, ob->sa.p, m, text_d + end, t, 1, gt_cur, end, nbnd, b_d.p, sr.p);
+      cm.bcast(ctx, sr.p, (size_t)nbnd * 8, own);
     }
-    BlockMeta meta{0, 0, 0};
-    if (own == rank) {
-      meta = BlockMeta{ob->i0, ob->end_bit, (int)ob->last};
-      h2d(ctx, reinterpret_cast<BlockMeta *>(pack.p), &meta, 1);
-      // K5 for everybody's walkers: the rank of suffix(end + b) among the block's suffixes
-      if (nbnd > 0)
-        initial_ranks(ctx, text_d + beg, ob->sa.p, m, text_d + end, t, 1, gt_cur, end, nbnd, b_d.p, sr_p);
-      PSC_CUDA(cudaMemcpyAsync(gtb_p, ob->gtb.p, gtb_bytes, cudaMemcpyDeviceToDevice, ctx->stream));
-      if (t > 0) PSC_CUDA(cudaMemcpyAsync(bwt_p, ob->bwt.p, (size_t)m, cudaMemcpyDeviceToDevice, ctx->stream));
-      sync(ctx);  // `meta` is a stack variable
-      pcs.sa[id] = std::move(ob->sa);
-      mine[id].reset();  // BWT and bits now live in the packed copy
-    }
-    cm.bcast(ctx, pack.p, total, own);
-    if (world > 1) { d2h(ctx, &meta, reinterpret_cast<BlockMeta *>(pack.p), 1); sync(ctx); }
+    feeder.release();
+    BlockFeed *feed;  // [meta | gt_begin bits | BWT] and the rank structure, prepared ahead
+    { HostTrace ht(ctx, "dist_feed_wait(host)"); feed = feeder.get(id); }
+    const BlockMeta meta = feed->meta;
+    const PackLayout lay(m, t > 0);
+    const uint32_t *gtb_p = reinterpret_cast<const uint32_t *>(feed->pack + lay.gtb_off);
+    const uint64_t *sr_p = sr.p;
     const long i0 = (long)meta.i0;
     PSC_CUDA(cudaMemsetAsync(gt_new, 0, gwords * 4, ctx->stream));
+    BlockFeeder::Job post;
+    bool acquired = false;
     if (t > 0) {
       const long per = (div_up(m + 1, (long)world) + 3) / 4 * 4;
       pcs.per[id] = per;
       DevBuf<uint32_t> gap_full(ctx, (size_t)per * world);
       gap_full.zero();
-      psc_rank *rk = rank_build(ctx, bwt_p, m, i0);
-      try {
-        uint64_t Cmap[256], run = 0;
-        for (int c = 0; c < 256; ++c) { Cmap[c] = run; run += (uint64_t)rk->counts[c] + (c == meta.last ? 1 : 0); }
-        const WalkPlan &p = plans[rank];
-        if (p.b.size() > 1)  // walker k of my plan starts from the rank of boundary k + 1
-          walk_with_plan(ctx, rk, i0, (uint8_t)meta.last, Cmap, text_d + end, p, b_d.p + off[rank], sr_p + off[rank] + 1,
-                         gt_cur, end, id > 0 ? gt_new : nullptr, gap_full.p);
-      } catch (...) { rank_free(rk); throw; }
-      rank_free(rk);
-      // per-GPU gap counts summed, every rank keeps a slice
-      pcs.gap[id].alloc(ctx, per);
-      bool as_bytes = false;
-      if (world > 1 && !getenv("PSC_GAP_RS32")) {
-        // 1 byte per counter over NVLink instead of 4 when no sum can reach 256 (largest local count * ranks < 256)
-        DevBuf<uint8_t> narrow(ctx, (size_t)per * world), slice8(ctx, per);
-        DevBuf<uint32_t> vmax(ctx, 1);
-        vmax.zero();
-        const long n4 = per * world / 4;
-        narrow_u32_to_u8_kernel<<<(unsigned)div_up(n4, 256), 256, 0, ctx->stream>>>(gap_full.p, n4, reinterpret_cast<uint32_t *>(narrow.p), vmax.p);
-        PSC_LAUNCH_CHECK();
-        cm.allreduce_max_u32(ctx, vmax.p, 1);
-        uint32_t hmax = 0;
-        d2h(ctx, &hmax, vmax.p, 1);
-        sync(ctx);
-        if ((uint64_t)hmax * (uint64_t)world < 256) {
-          cm.reduce_scatter_u8(ctx, narrow.p, slice8.p, (size_t)per);
-          widen_u8_to_u32_kernel<<<(unsigned)div_up(per / 4, 256), 256, 0, ctx->stream>>>(reinterpret_cast<const uint32_t *>(slice8.p), per / 4, pcs.gap[id].p);
-          PSC_LAUNCH_CHECK();
-          ctx->launches += 2;
-          as_bytes = true;
-        }
-      }
-      if (!as_bytes) cm.reduce_scatter_u32(ctx, gap_full.p, pcs.gap[id].p, (size_t)per);
-      const long cnt = std::max(0L, std::min(per, m + 1 - per * rank));
-      pcs.carry[id].alloc(ctx, coarse_carry_tiles(cnt) + 1);
-      coarse_carries_u32(ctx, pcs.gap[id].p, cnt, pcs.carry[id].p);
-      PSC_CUDA(cudaMemcpyAsync(my_tot.p + id, pcs.carry[id].p + coarse_carry_tiles(cnt), 8, cudaMemcpyDeviceToDevice, ctx->stream));
-      // new gt words of disjoint word ranges
-      if (id > 0 && world > 1)
+      const psc_rank *rk = feed->rk;
+      uint64_t Cmap[256], run = 0;
+      for (int c = 0; c < 256; ++c) { Cmap[c] = run; run += (uint64_t)rk->counts[c] + (c == meta.last ? 1 : 0); }
+      const WalkPlan &p = plans[rank];
+      if (p.b.size() > 1)  // walker k of my plan starts from the rank of boundary k + 1
+        walk_with_plan(ctx, rk, i0, (uint8_t)meta.last, Cmap, text_d + end, p, b_d.p + off[rank], sr_p + off[rank] + 1,
+                       gt_cur, end, id > 0 ? gt_new : nullptr, gap_full.p);
+      // new gt words of disjoint word ranges: the next block's start ranks and walk need them
+      { HostTrace ht(ctx, "dist_turn_wait(host)"); feeder.acquire(step, 1); }
+      acquired = true;
+      if (id > 0 && world > 1) {
+        KTrace kt(ctx, "dist_gt_allgather");
         cm.allgather(ctx, gt_new + sh.wl + sh.per_w * rank, gt_new + sh.wl, (size_t)sh.per_w * 4);
+      }
+      // per-GPU gap counts summed, every rank keeps a slice: nothing needs it before the final merge, so the
+      // helper does it while the next block is walked
+      auto counts = std::make_shared<DevBuf<uint32_t>>(std::move(gap_full));
+      uint64_t *tot_p = my_tot.p + id;
+      post = [counts, per, m, id, tot_p, &pcs](psc_context *c, Comm &hc) {  // runs in one of the helper's turns
+        const int world = hc.world, rank = hc.rank;
+        pcs.gap[id].alloc(c, per);
+        bool as_bytes = false;
+        if (world > 1 && !getenv("PSC_GAP_RS32")) {
+          // 1 byte per counter over NVLink instead of 4 when no sum can reach 256 (largest local count * ranks < 256)
+          DevBuf<uint8_t> narrow(c, (size_t)per * world), slice8(c, per);
+          DevBuf<uint32_t> vmax(c, 1);
+          vmax.zero();
+          const long n4 = per * world / 4;
+          narrow_u32_to_u8_kernel<<<(unsigned)div_up(n4, 256), 256, 0, c->stream>>>(counts->p, n4, reinterpret_cast<uint32_t *>(narrow.p), vmax.p);
+          PSC_LAUNCH_CHECK();
+          hc.allreduce_max_u32(c, vmax.p, 1);
+          uint32_t hmax = 0;
+          d2h(c, &hmax, vmax.p, 1);
+          sync(c);
+          if ((uint64_t)hmax * (uint64_t)world < 256) {
+            hc.reduce_scatter_u8(c, narrow.p, slice8.p, (size_t)per);
+            widen_u8_to_u32_kernel<<<(unsigned)div_up(per / 4, 256), 256, 0, c->stream>>>(reinterpret_cast<const uint32_t *>(slice8.p), per / 4, pcs.gap[id].p);
+            PSC_LAUNCH_CHECK();
+            c->launches += 2;
+            as_bytes = true;
+          }
+        }
+        if (!as_bytes) hc.reduce_scatter_u32(c, counts->p, pcs.gap[id].p, (size_t)per);
+        const long cnt = std::max(0L, std::min(per, m + 1 - per * rank));
+        pcs.carry[id].alloc(c, coarse_carry_tiles(cnt) + 1);
+        coarse_carries_u32(c, pcs.gap[id].p, cnt, pcs.carry[id].p);
+        PSC_CUDA(cudaMemcpyAsync(tot_p, pcs.carry[id].p + coarse_carry_tiles(cnt), 8, cudaMemcpyDeviceToDevice, c->stream));
+        sync(c);  // the counters go back to the cache of the context they came from
+      };
     }
     if (id > 0) {
       if (m > 1) {
@@ -281,7 +484,16 @@ static void dist_blocks(psc_context *ctx, Comm &cm, const uint8_t *text_d, long 
       ctx->launches += 2;
     }
     std::swap(gt_cur, gt_new);
+    sync(ctx);  // the feed's buffers go back to the helper
+    if (!acquired) feeder.acquire(step, 1);
+    feeder.done(id, std::move(post));
+    feeder.release();
+    if (own == rank) {
+      pcs.sa[id] = std::move(ob->sa);
+      mine[id].reset();
+    }
   }
+  { HostTrace ht(ctx, "dist_finish_wait(host)"); feeder.finish(); }
   // slice totals of all ranks
   if (world > 1) cm.allgather(ctx, my_tot.p, totals_d.p, (size_t)B * 8);
   else PSC_CUDA(cudaMemcpyAsync(totals_d.p, my_tot.p, (size_t)B * 8, cudaMemcpyDeviceToDevice, ctx->stream));
@@ -468,31 +680,56 @@ int psc_dist_unique_id(uint8_t id[128]) {
   return nccl_unique_id(id);
 }
 
+static void dist_teardown(psc_context *ctx, bool abort) {
+  if (ctx->comm) {
+    if (abort) nccl_comm_abort(ctx->comm); else nccl_comm_destroy(ctx->comm);
+    if (!abort) { delete ctx->comm; ctx->comm = nullptr; }
+  }
+  if (!abort && ctx->helper) { psc_shutdown(ctx->helper); ctx->helper = nullptr; }
+}
+
 int psc_dist_init(psc_context *ctx, const uint8_t id[128], int rank, int world) {
   if (!ctx || world < 1 || rank < 0 || rank >= world || (world > 1 && !id)) { set_error("psc_dist_init: bad argument"); return PSC_EARG; }
   cudaSetDevice(ctx->device);
-  if (ctx->comm) { nccl_comm_destroy(ctx->comm); delete ctx->comm; ctx->comm = nullptr; }
+  dist_teardown(ctx, false);
   Comm *c = new Comm();
   int rc = nccl_comm_init(c, id, rank, world);
   if (rc != PSC_OK) { delete c; return rc; }
+  // PSC_DIST_HELPER=1: second stream + buffer cache for a thread that prepares the next blocks during a walk
+  // (BlockFeeder).  Off by default: measured on 2 GPUs it costs more than it hides.
+  psc_context *h = nullptr;
+  if (const char *e = getenv("PSC_DIST_HELPER")) {
+    if (atoi(e) != 0) {
+      rc = psc_init(ctx->device, 0, &h);
+      if (rc != PSC_OK) { nccl_comm_destroy(c); delete c; return rc; }
+      h->trace = false;
+      // lowest priority: a walker CTA that starts late ends late, and the walk lasts as long as its last walker
+      int least = 0, greatest = 0;
+      cudaDeviceGetStreamPriorityRange(&least, &greatest);
+      cudaStream_t low = nullptr;
+      if (cudaStreamCreateWithPriority(&low, cudaStreamNonBlocking, least) == cudaSuccess) {
+        cudaStreamDestroy(h->stream);
+        h->stream = low;
+      }
+    }
+  }
   ctx->comm = c;
+  ctx->helper = h;
   return PSC_OK;
 }
 
 int psc_dist_finalize(psc_context *ctx) {
   if (!ctx) return PSC_OK;
-  if (ctx->comm) {
+  if (ctx->comm || ctx->helper) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    nccl_comm_destroy(ctx->comm);
-    delete ctx->comm;
-    ctx->comm = nullptr;
+    dist_teardown(ctx, false);
   }
   return PSC_OK;
 }
 
 int psc_dist_abort(psc_context *ctx) {
-  if (ctx && ctx->comm) nccl_comm_abort(ctx->comm);
+  if (ctx) dist_teardown(ctx, true);
   return PSC_OK;
 }
 
