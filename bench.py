@@ -243,22 +243,34 @@ def cpu_sample_baseline(text, n_blocks, sample_n):
     return cb
 
 
-def walk_roofline(s, r32, peak, peak_src):
-    """roofline of the LF-walk phase (K5 excluded): emit + partition + accumulate kernels, 41.25 algorithmic
-    bytes per step against the random 32-byte sector rate R32 measured in this run"""
-    steps_s = s["lf_steps"] / (s["ms_walk"] / 1e3)
-    roof = {"kernel": "lf_walk_kernel (whole walk phase: rank emit + range partition + gap accumulate)",
-            "bound": "hbm", "unit": "GB/s", "achieved": 41.25 * steps_s / 1e9,
-            "algorithmic_bytes_per_unit": 41.25, "units": "LF steps", "units_per_step": s["lf_steps"],
-            "lf_steps_per_s": steps_s, "ms_walk_per_step": s["ms_walk"],
-            "hbm_copy_peak": peak, "hbm_copy_peak_source": peak_src, "traffic": None}
-    if r32:
-        roof["peak"] = r32
-        roof["peak_source"] = ("R32: independent random 32-byte sector reads over a 16 GiB buffer, full-occupancy grid, "
-                               "measured in this run (psc_bench_random_sectors)")
+def walk_roofline(s, r32, r32_ws, ws_bytes, peak, peak_src):
+    """roofline of the dominant kernel, lf_walk_kernel (K6) alone: every LF step reads ONE random 32-byte sector of
+    the block's rank planes (plus 5.25 sequential bytes: 1 text symbol, a gt bit in and out, the 4-byte rank it
+    leaves in a page).  The ceiling is the rate of independent random 32-byte sector reads over a buffer of the
+    SAME size as the rank planes (so that the share the 126 MB L2 serves is the same), measured in this run;
+    the rate over a 16 GiB buffer (no L2 share) is reported beside it.  The whole walk phase (kernel + grouping
+    and counting of the emitted ranks) is reported as lf_steps_per_s."""
+    k_ms = s.get("ms_walk_kernel") or s["ms_walk"]
+    steps_s = s["lf_steps"] / (k_ms / 1e3)
+    n_launch = max(1, s["n_blocks"] - 1)
+    roof = {"kernel": "lf_walk_kernel<3> (LF walk, ranks leave in per-bucket pages)",
+            "bound": "hbm", "unit": "GB/s", "achieved": 32.0 * steps_s / 1e9,
+            "algorithmic_bytes_per_unit": 32.0, "sequential_bytes_per_unit": 5.25,
+            "units": "LF steps (one random 32-byte sector each)", "units_per_step": s["lf_steps"],
+            "kernel_ms_per_step": k_ms, "avg_launch_ms": k_ms / n_launch, "lf_steps_per_s_kernel": steps_s,
+            "walk_phase_ms_per_step": s["ms_walk"], "working_set_bytes": ws_bytes,
+            "hbm_copy_peak": peak, "hbm_copy_peak_source": peak_src,
+            "frac_of_copy_peak": 37.25 * steps_s / 1e9 / peak, "traffic": None}
+    ceiling = r32_ws or r32
+    if ceiling:
+        roof["peak"] = ceiling
+        roof["peak_source"] = ("independent random 32-byte sector reads over a %d MiB buffer (the size of the block's rank planes), "
+                               "full-occupancy grid, measured in this run (psc_bench_random_sectors)" % (ws_bytes >> 20)
+                               if r32_ws else "R32 over a 16 GiB buffer, measured in this run (psc_bench_random_sectors)")
         roof["r32_gbs"] = r32
-        roof["steps_per_s_bound"] = r32 * 1e9 / 41.25
-        roof["frac"] = roof["achieved"] / r32
+        roof["r32_working_set_gbs"] = r32_ws
+        roof["steps_per_s_bound"] = ceiling * 1e9 / 32.0
+        roof["frac"] = roof["achieved"] / ceiling
     else:
         roof["peak"] = peak
         roof["peak_source"] = peak_src
@@ -288,7 +300,8 @@ def add_traffic(roof, s, pair_b=0, launches=1):
     """DRAM bytes of one launch from the committed ncu --set full capture (profiles/), scaled to the
     algorithmic bytes of an average launch of this run"""
     try:
-        tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+        name = "r2_traffic.json" if os.path.exists(os.path.join(ROOT, "profiles", "r2_traffic.json")) else "r1_traffic.json"
+        tr = json.load(open(os.path.join(ROOT, "profiles", name)))
         key = "lf_walk_kernel" if roof["kernel"].startswith("lf_walk") else "radix_pass_kernel"
         k = tr[key]
         units = s["lf_steps"] / max(1, s["n_blocks"] - 1) if key == "lf_walk_kernel" else pair_b / 24.0 / launches
@@ -482,14 +495,18 @@ def main():
                 "phases_ms": {k: s[k] for k in s if k.startswith("ms_")},
                 "counters": {k: s[k] for k in s if not k.startswith("ms_")}}
         if s["lf_steps"] > 0:
-            r32 = None
+            r32 = r32_ws = None
+            # the walk's working set: the rank planes of one block, 32 bytes per 224 positions and symbol
+            sigma = int(np.count_nonzero(np.bincount(text[:min(n, 1 << 24)], minlength=256)))
+            ws_bytes = sigma * (min(n, max_block) // 224 + 1) * 32
             try:   # random 32-byte sector rate of this GPU (SURVEY 8-d "R32"), the walk's ceiling
                 r32 = ctx.bench_random_sectors(16 << 30, 128)
+                r32_ws = ctx.bench_random_sectors(max(ws_bytes, 1 << 20), 128)
             except Exception as e:
                 line["r32_error"] = str(e)[:100]
             # LF steps of the whole job per second of its walk phase (at N > 1: rank 0's share, same wall time)
             total_steps = sum(max(0, n - min(n, (i + 1) * max_block)) for i in range(s["n_blocks"]))
-            roof = walk_roofline(s, r32, peak, peak_src)
+            roof = walk_roofline(s, r32, r32_ws, ws_bytes, peak, peak_src)
             add_traffic(roof, s)
             line["lf_steps_per_s"] = total_steps / (s["ms_walk"] / 1e3)
             line["lf_steps_per_step"] = total_steps

@@ -174,6 +174,8 @@ typedef struct psc_stats {
                      * keys-only pass, 1 in for a pass that builds its keys from the text */
   long radix_keygen_bytes; /* the share of radix_bytes moved by key-building passes ... */
   double ms_radix_keygen;  /* ... and their share of ms_radix_pass */
+  double ms_walk_kernel;   /* device time of the LF-walk kernels alone (events around each launch); ms_walk also
+                            * holds the grouping and counting of the ranks they emit */
 } psc_stats;
 int psc_get_stats(psc_context *ctx, psc_stats *out);
 

@@ -97,7 +97,102 @@ struct WalkTables {
 // traffic per step instead of 64 B of random traffic.  (The reference partitions its gap buffers
 // by value range for another reason -- lock-free CPU updaters, stream.hpp:160-232.)
 //   MODE 0: RED on gap[i]   1: warp-aggregated RED (match.any)   2: emit ranks + bucket counts
+//   MODE 3: the partition folded into the walk.  Every warp keeps a 32-entry buffer per bucket in shared memory;
+//   the ranks of a step go to their buckets (lanes of one bucket found with match.any), a buffer that fills up
+//   leaves as one 128-byte PAGE (pages are handed out 16 at a time per warp from one global counter) and a
+//   descriptor (bucket << 25 | page) is written for it.  Afterwards only the descriptors are grouped by bucket
+//   (1/32 of the elements) and the pages are counted bucket by bucket.  The bookkeeping of a step runs between
+//   the issue of the next step's sector load and its use, where the walker would wait anyway.
 constexpr int WK_MAX_BUCKETS = 512;
+constexpr int WK_PAGE_BUCKETS = 72;   // MODE 3: at most this many buckets (9.3 KB of buffers per warp)
+constexpr int WK_PAGE_BATCH = 16;     // pages a warp takes from the global counter at once
+constexpr int WK_PAGE_ID_BITS = 25;
+
+struct PagedOut {
+  uint32_t *pages;                  // [cap_pages][32]
+  uint32_t *desc;                   // [cap_pages]
+  unsigned long long *next_page;    // global page counter
+  uint32_t cap_pages;
+};
+
+// the sector of (code, i): issued early, counted later
+__device__ __forceinline__ void rank_occ_issue(const RankView &rv, int code, uint32_t i, uint32_t (&w)[8]) {
+  const uint32_t s = i / RK_BITS;
+  const uint32_t *p = rv.sectors + ((size_t)code * (size_t)rv.n_sectors + s) * 8;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::64B.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+               : "l"(p));
+}
+__device__ __forceinline__ uint32_t rank_occ_finish(uint32_t i, const uint32_t (&w)[8]) {
+  const uint32_t r = i % RK_BITS;
+  uint32_t cnt = w[0];
+#pragma unroll
+  for (int k = 0; k < 7; ++k) {
+    int nb = (int)r - 32 * k;
+    nb = nb < 0 ? 0 : (nb > 32 ? 32 : nb);
+    const uint32_t mask = nb == 32 ? 0xffffffffu : ((1u << nb) - 1u);
+    cnt += __popc(w[k + 1] & mask);
+  }
+  return cnt;
+}
+
+// MODE 3 bookkeeping of one warp step: `v` = this lane's rank (valid lanes only)
+struct WarpPager {
+  uint32_t *buf;   // [n_buckets][32] of this warp
+  uint32_t *cnt;   // [n_buckets]
+  uint32_t next = 0, end = 0;  // the warp's batch of pages (uniform over the lanes)
+  __device__ __forceinline__ uint32_t take_page(const PagedOut &po, int lane) {
+    if (next == end) {
+      unsigned long long p = 0;
+      if (lane == 0) p = atomicAdd(po.next_page, (unsigned long long)WK_PAGE_BATCH);
+      next = (uint32_t)__shfl_sync(0xffffffffu, p, 0);
+      end = next + WK_PAGE_BATCH;
+    }
+    return next++;
+  }
+  __device__ __forceinline__ void put(const PagedOut &po, uint32_t *sB, bool valid, uint32_t v, int bshift, int lane) {
+    const uint32_t b = valid ? (v >> bshift) : (0x80000000u | (uint32_t)lane);
+    const uint32_t peers = __match_any_sync(0xffffffffu, b);
+    const int lead = __ffs(peers) - 1;
+    uint32_t have = 0;
+    if (valid && lane == lead) have = cnt[b];
+    have = __shfl_sync(0xffffffffu, have, lead);
+    const uint32_t slot = have + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+    const uint32_t total = have + (uint32_t)__popc(peers);
+    if (valid && slot < 32) buf[b * 32 + slot] = v;
+    __syncwarp();
+    uint32_t fullm = __ballot_sync(0xffffffffu, valid && lane == lead && total >= 32);
+    while (fullm) {
+      const int L = __ffs(fullm) - 1;
+      fullm &= fullm - 1;
+      const uint32_t bb = __shfl_sync(0xffffffffu, b, L);
+      const uint32_t page = take_page(po, lane);
+      if (page < po.cap_pages) {
+        po.pages[(size_t)page * 32 + lane] = buf[bb * 32 + lane];
+        if (lane == 0) { po.desc[page] = (bb << WK_PAGE_ID_BITS) | page; atomicAdd(&sB[bb], 1u); }
+      }
+      __syncwarp();
+      if (valid && b == bb && slot >= 32) buf[bb * 32 + slot - 32] = v;  // the entries that did not fit
+    }
+    if (valid && lane == lead) cnt[b] = total >= 32 ? total - 32 : total;
+    __syncwarp();
+  }
+  // end of the kernel: partly filled buffers leave as padded pages, unused pages of the batch get a descriptor
+  // of the extra bucket `n_buckets`
+  __device__ __forceinline__ void drain(const PagedOut &po, uint32_t *sB, int n_buckets, int lane) {
+    for (int b = 0; b < n_buckets; ++b) {
+      const uint32_t c = cnt[b];
+      if (c == 0) continue;
+      const uint32_t page = take_page(po, lane);
+      if (page < po.cap_pages) {
+        po.pages[(size_t)page * 32 + lane] = (uint32_t)lane < c ? buf[b * 32 + lane] : 0xffffffffu;
+        if (lane == 0) { po.desc[page] = ((uint32_t)b << WK_PAGE_ID_BITS) | page; atomicAdd(&sB[b], 1u); }
+      }
+    }
+    for (uint32_t page = next + lane; page < end; page += 32)
+      if (page < po.cap_pages) { po.desc[page] = ((uint32_t)n_buckets << WK_PAGE_ID_BITS) | page; atomicAdd(&sB[n_buckets], 1u); }
+  }
+};
 
 template <int MODE>
 __global__ void __launch_bounds__(256)
@@ -106,15 +201,23 @@ __global__ void __launch_bounds__(256)
                    const uint64_t *__restrict__ start_rank, const uint32_t *__restrict__ gt_in,
                    long gt_in_off, uint32_t *__restrict__ gt_out, long gt_out_off,
                    uint32_t *__restrict__ gap, uint32_t *__restrict__ emit, long emit_base, int bshift,
-                   int n_buckets, unsigned long long *__restrict__ bucket_count) {
+                   int n_buckets, unsigned long long *__restrict__ bucket_count, PagedOut po) {
+  extern __shared__ uint32_t dyn_smem[];  // MODE 3: per warp n_buckets * 33 words
   __shared__ uint32_t sC[256];
   __shared__ int16_t sCode[256];
-  __shared__ uint32_t sB[MODE == 2 ? WK_MAX_BUCKETS : 1];
+  __shared__ uint32_t sB[MODE == 2 ? WK_MAX_BUCKETS : (MODE == 3 ? WK_PAGE_BUCKETS + 1 : 1)];
   sC[threadIdx.x] = tables->C[threadIdx.x];
   sCode[threadIdx.x] = tables->code[threadIdx.x];
   if (MODE == 2) for (int b = threadIdx.x; b < n_buckets; b += 256) sB[b] = 0;
-  __syncthreads();
   const int lane = threadIdx.x & 31;
+  WarpPager pager;
+  if (MODE == 3) {
+    for (int b = threadIdx.x; b <= n_buckets; b += 256) sB[b] = 0;
+    pager.buf = dyn_smem + (size_t)(threadIdx.x >> 5) * n_buckets * 33;
+    pager.cnt = pager.buf + n_buckets * 32;
+    for (int b = lane; b < n_buckets; b += 32) pager.cnt[b] = 0;
+  }
+  __syncthreads();
   long w = (long)blockIdx.x * blockDim.x + threadIdx.x;
   long s = 0, e = 0;
   uint32_t i = 0;
@@ -128,8 +231,47 @@ __global__ void __launch_bounds__(256)
   uint4 tb = make_uint4(0, 0, 0, 0);
   long cur_in_w = -1, cur_out_w = -1;
   uint32_t in_word = 0, out_word = 0;
+  uint32_t prev = 0;
+  bool prev_valid = false;
   for (long k = 0; k < max_steps; ++k) {
     const bool active = k < steps;
+    if (MODE == 3) {
+      // same step as below, with the previous step's rank put away while the sector is on its way
+      uint32_t w8[8];
+      int c = 0, code = -1;
+      uint32_t gin = 0;
+      if (active) {
+        uintptr_t a = (uintptr_t)(tail + j - 1);
+        uintptr_t ch = a & ~(uintptr_t)15;
+        if (ch != cur_chunk) { tb = *reinterpret_cast<const uint4 *>(ch); cur_chunk = ch; }
+        uint32_t b = (uint32_t)(a & 15);
+        uint32_t word = (b & 8) ? ((b & 4) ? tb.w : tb.z) : ((b & 4) ? tb.y : tb.x);
+        c = (int)((word >> ((b & 3) * 8)) & 255u);
+        long ob = gt_out_off + j - 1;
+        if (gt_out) {
+          if ((ob >> 5) != cur_out_w) {
+            if (cur_out_w >= 0 && out_word) atomicOr(&gt_out[cur_out_w], out_word);
+            cur_out_w = ob >> 5;
+            out_word = 0;
+          }
+          if (i > i0) out_word |= 1u << (ob & 31);
+        }
+        long ib = gt_in_off + j - 1;
+        if ((ib >> 5) != cur_in_w) { cur_in_w = ib >> 5; in_word = gt_in ? gt_in[cur_in_w] : 0u; }
+        gin = (in_word >> (ib & 31)) & 1u;
+        code = sCode[c];
+        if (code >= 0) rank_occ_issue(rv, code, i, w8);
+      }
+      pager.put(po, sB, prev_valid, prev, bshift, lane);
+      if (active) {
+        const uint32_t occ = code >= 0 ? rank_occ_finish(i, w8) : 0u;
+        i = sC[c] + occ + ((c == last) ? gin : 0u);
+        --j;
+      }
+      prev = i;
+      prev_valid = active;
+      continue;
+    }
     if (active) {
       // symbol tail[j-1]
       uintptr_t a = (uintptr_t)(tail + j - 1);
@@ -170,11 +312,29 @@ __global__ void __launch_bounds__(256)
     }
   }
   if (gt_out && cur_out_w >= 0 && out_word) atomicOr(&gt_out[cur_out_w], out_word);
+  if (MODE == 3) {
+    pager.put(po, sB, prev_valid, prev, bshift, lane);
+    pager.drain(po, sB, n_buckets, lane);
+    __syncthreads();
+    for (int b = threadIdx.x; b <= n_buckets; b += 256)
+      if (sB[b]) atomicAdd(&bucket_count[b], (unsigned long long)sB[b]);
+  }
   if (MODE == 2) {
     __syncthreads();
     for (int b = threadIdx.x; b < n_buckets; b += 256)
       if (sB[b]) atomicAdd(&bucket_count[b], (unsigned long long)sB[b]);
   }
+}
+
+// pages grouped by bucket (descriptors in bucket order): one warp per page, padding entries skipped
+__global__ void __launch_bounds__(256)
+    page_accumulate_kernel(const uint32_t *__restrict__ desc, long n_pages, const uint32_t *__restrict__ pages,
+                           uint32_t *__restrict__ gap) {
+  const long w = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (w >= n_pages) return;
+  const uint32_t page = desc[w] & ((1u << WK_PAGE_ID_BITS) - 1u);
+  const uint32_t v = pages[(size_t)page * 32 + (threadIdx.x & 31)];
+  if (v != 0xffffffffu) atomicAdd(&gap[v], 1u);
 }
 
 // ranks -> buckets (order inside a bucket is irrelevant: they are only counted afterwards)
@@ -264,7 +424,66 @@ void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, con
   int use = mode;
   if (use < 0) use = ((size_t)(r->m + 1) * 4 > (size_t)(24 << 20) && hi - lo >= (1 << 20)) ? 2 : 0;
   unsigned blocks = (unsigned)div_up(nwalk, 256);
-  if (use == 2) {
+  // device time of the walk kernel alone: every branch below synchronises after it anyway
+  struct KernelClock {
+    psc_context *c; cudaEvent_t a = nullptr, b = nullptr;
+    explicit KernelClock(psc_context *ctx) : c(ctx) { cudaEventCreate(&a); cudaEventCreate(&b); }
+    void start() { cudaEventRecord(a, c->stream); }
+    void stop() { cudaEventRecord(b, c->stream); }
+    ~KernelClock() {
+      float ms = 0;
+      if (cudaEventSynchronize(b) == cudaSuccess && cudaEventElapsedTime(&ms, a, b) == cudaSuccess) c->stats.ms_walk_kernel += ms;
+      else cudaGetLastError();
+      cudaEventDestroy(a); cudaEventDestroy(b);
+    }
+  } kclock(ctx);
+  if (use == 2 && mode < 0 && hi - lo <= (1L << 29)) {
+    // partition folded into the walk when the gap array splits into few enough L2-sized buckets
+    int bs = 22;
+    while (bs < 24 && ((r->m + 1) >> bs) + 1 > WK_PAGE_BUCKETS) ++bs;
+    if (((r->m + 1) >> bs) + 1 <= WK_PAGE_BUCKETS) use = 3;
+  }
+  if (use == 3) {
+    const long T = hi - lo;
+    int bshift = 22;
+    while (((r->m + 1) >> bshift) + 1 > WK_PAGE_BUCKETS) ++bshift;
+    const int nb = (int)(((r->m + 1) >> bshift) + 1);
+    const long n_warps = (long)blocks * 8;
+    // every entry leaves in exactly one page: full pages, one padded page per warp and bucket at the end, and
+    // the unused rest of every warp's last batch
+    const long cap_pages = T / 32 + n_warps * (nb + WK_PAGE_BATCH) + WK_PAGE_BATCH;
+    if (cap_pages >= (1L << WK_PAGE_ID_BITS)) { set_error("lf_walk: %ld pages do not fit the descriptor", cap_pages); throw CudaError{PSC_ECUDA}; }
+    long scratch = 1L << 24;  // size classes as in mode 2 (see there)
+    while (scratch < cap_pages * 32) scratch <<= 1;
+    DevBuf<uint32_t> pages(ctx, scratch), desc(ctx, scratch / 32), sorted(ctx, scratch / 32);
+    DevBuf<unsigned long long> bc(ctx, WK_MAX_BUCKETS + 1), cur(ctx, WK_MAX_BUCKETS);
+    bc.zero();
+    PagedOut po{pages.p, desc.p, bc.p + WK_MAX_BUCKETS, (uint32_t)cap_pages};
+    const size_t smem = (size_t)8 * nb * 33 * 4;
+    PSC_CUDA(cudaFuncSetAttribute(lf_walk_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kclock.start();
+    { KTrace kt(ctx, "lf_walk(paged)"); lf_walk_kernel<3><<<blocks, 256, smem, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d, start_rank_d,
+                                                        gt_in_bits_d, gt_in_off, gt_out_bits_d, gt_out_off, gap_d,
+                                                        nullptr, lo, bshift, nb, bc.p, po); }
+    kclock.stop();
+    PSC_LAUNCH_CHECK();
+    unsigned long long h[WK_MAX_BUCKETS + 1], c[WK_MAX_BUCKETS];
+    d2h(ctx, h, bc.p, WK_MAX_BUCKETS + 1);
+    sync(ctx);
+    const long n_taken = (long)h[WK_MAX_BUCKETS];
+    if (n_taken > cap_pages) { set_error("lf_walk: %ld pages taken, %ld reserved", n_taken, cap_pages); throw CudaError{PSC_ECUDA}; }
+    unsigned long long run = 0;
+    for (int b = 0; b <= nb; ++b) { c[b] = run; run += h[b]; }
+    if ((long)run != n_taken) { set_error("lf_walk: %llu page descriptors for %ld pages", run, n_taken); throw CudaError{PSC_ECUDA}; }
+    h2d(ctx, cur.p, c, nb + 1);
+    { KTrace kt(ctx, "page_partition"); rank_partition_kernel<<<(unsigned)div_up(n_taken, PT_TILE), PT_THREADS, 0, ctx->stream>>>(desc.p, n_taken, WK_PAGE_ID_BITS, nb + 1, cur.p, sorted.p); }
+    PSC_LAUNCH_CHECK();
+    const long n_real = (long)c[nb];  // the descriptors of unused pages come last
+    { KTrace kt(ctx, "page_accumulate"); page_accumulate_kernel<<<(unsigned)div_up(n_real * 32, 256), 256, 0, ctx->stream>>>(sorted.p, n_real, pages.p, gap_d); }
+    PSC_LAUNCH_CHECK();
+    sync(ctx);
+    ctx->launches += 3;
+  } else if (use == 2) {
     const long T = hi - lo;
     int bshift = 22;  // 4 Mi counters = 16 MB of gap array per bucket
     while (((r->m + 1) >> bshift) + 1 > WK_MAX_BUCKETS) ++bshift;
@@ -277,9 +496,11 @@ void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, con
     DevBuf<uint32_t> emit(ctx, scratch), part(ctx, scratch);
     DevBuf<unsigned long long> bc(ctx, WK_MAX_BUCKETS), cur(ctx, WK_MAX_BUCKETS);
     bc.zero();
+    kclock.start();
     { KTrace kt(ctx, "lf_walk(emit)"); lf_walk_kernel<2><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d, start_rank_d,
                                                         gt_in_bits_d, gt_in_off, gt_out_bits_d, gt_out_off, gap_d,
-                                                        emit.p, lo, bshift, nb, bc.p); }
+                                                        emit.p, lo, bshift, nb, bc.p, PagedOut{}); }
+    kclock.stop();
     PSC_LAUNCH_CHECK();
     unsigned long long h[WK_MAX_BUCKETS], c[WK_MAX_BUCKETS];
     d2h(ctx, h, bc.p, nb);
@@ -295,14 +516,16 @@ void lf_walk(psc_context *ctx, const psc_rank *r, uint32_t i0, uint8_t last, con
     sync(ctx);
     ctx->launches += 3;
   } else {
+    kclock.start();
     if (use == 1)
       lf_walk_kernel<1><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d, start_rank_d,
                                                           gt_in_bits_d, gt_in_off, gt_out_bits_d, gt_out_off, gap_d,
-                                                          nullptr, 0, 0, 0, nullptr);
+                                                          nullptr, 0, 0, 0, nullptr, PagedOut{});
     else
       { KTrace kt(ctx, "lf_walk(red)"); lf_walk_kernel<0><<<blocks, 256, 0, ctx->stream>>>(rv, i0, last, tb_d.p, tail_d, nwalk, walk_beg_d, start_rank_d,
                                                           gt_in_bits_d, gt_in_off, gt_out_bits_d, gt_out_off, gap_d,
-                                                          nullptr, 0, 0, 0, nullptr); }
+                                                          nullptr, 0, 0, 0, nullptr, PagedOut{}); }
+    kclock.stop();
     PSC_LAUNCH_CHECK();
     sync(ctx);  // tb is a stack object
     ctx->launches++;

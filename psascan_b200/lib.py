@@ -32,7 +32,7 @@ class Stats(C.Structure):
         "ms_total", "ms_gt_end", "ms_sort", "ms_radix", "ms_bwt", "ms_rank_build", "ms_init_ranks",
         "ms_walk", "ms_merge", "ms_h2d", "ms_d2h", "ms_radix_pass")] + [(k, C.c_long) for k in (
         "n_blocks", "lf_steps", "radix_passes", "radix_elems", "doubling_rounds", "walkers",
-        "kernel_launches", "radix_bytes", "radix_keygen_bytes")] + [("ms_radix_keygen", C.c_double)]
+        "kernel_launches", "radix_bytes", "radix_keygen_bytes")] + [("ms_radix_keygen", C.c_double), ("ms_walk_kernel", C.c_double)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -290,10 +290,12 @@ def test_dist_schedule_single_rank(ctx):
             assert np.array_equal(d_out.cpu().numpy(), sa5), (name, mb)
 
 
-@pytest.mark.parametrize("env", [dict(PSC_WALK_MODE="1"), dict(PSC_WALK_MODE="2"), dict(PSC_WALK_CHUNK="4096"),
+@pytest.mark.parametrize("env", [dict(PSC_WALK_MODE="1"), dict(PSC_WALK_MODE="2"), dict(PSC_WALK_MODE="3"),
+                                 dict(PSC_WALK_MODE="3", PSC_WALK_CHUNK="2048", PSC_WALKERS="40"), dict(PSC_WALK_CHUNK="4096"),
                                  dict(PSC_WALKERS="7"), dict(PSC_MERGE_CHUNK="1000"), dict(PSC_BWT_SHIFT="8"),
                                  dict(PSC_MERGE_CHUNK="64", PSC_WALK_CHUNK="2048", PSC_WALK_MODE="2")],
-                         ids=["walk_warp_aggregated", "walk_emit_partition", "walk_multi_chunk", "seven_walkers",
+                         ids=["walk_warp_aggregated", "walk_emit_partition", "walk_paged", "walk_paged_chunks",
+                              "walk_multi_chunk", "seven_walkers",
                               "merge_small_chunks", "bwt_windowed", "all_small"])
 def test_env_selected_paths_subprocess(env):
     """Paths chosen by environment variables read once per process (the warp-aggregated and the
