@@ -50,8 +50,8 @@ __global__ void or_bits_shifted_kernel(uint32_t *dst, long dst_off, const uint32
 
 __global__ void set_bit_kernel(uint32_t *dst, long idx) { atomicOr(&dst[idx >> 5], 1u << (idx & 31)); }
 
-// Gap counters travel as bytes when they are small enough (they almost always are: a rank's counts of one block
-// average below one per entry): 4 entries per thread, the largest value seen goes to *vmax.
+// PSC_GAP_RS8=1: gap counters travel as bytes when they are small enough (they almost always are: a rank's counts
+// of one block average below one per entry): 4 entries per thread, the largest value seen goes to *vmax.
 __global__ void __launch_bounds__(256)
     narrow_u32_to_u8_kernel(const uint32_t *__restrict__ in, long n4, uint32_t *__restrict__ out4, uint32_t *vmax) {
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -447,8 +447,11 @@ static void dist_blocks(psc_context *ctx, Comm &cm, const uint8_t *text_d, long 
         const int world = hc.world, rank = hc.rank;
         pcs.gap[id].alloc(c, per);
         bool as_bytes = false;
-        if (world > 1 && !getenv("PSC_GAP_RS32")) {
-          // 1 byte per counter over NVLink instead of 4 when no sum can reach 256 (largest local count * ranks < 256)
+        if (world > 1 && getenv("PSC_GAP_RS8")) {
+          // opt-in: 1 byte per counter over NVLink instead of 4 when no sum can reach 256 (largest local count *
+          // ranks < 256).  Fewer bytes, yet measured SLOWER than the uint32 reduce-scatter (4 GPUs: 173.6 against
+          // 163.2 ms per 2 GiB construction, tools/dist_ab.py): NCCL sums uint32 at full NVLink speed, bytes not,
+          // and the width decision costs a small all-reduce and a host round trip per block.
           DevBuf<uint8_t> narrow(c, (size_t)per * world), slice8(c, per);
           DevBuf<uint32_t> vmax(c, 1);
           vmax.zero();
