@@ -196,8 +196,8 @@ static long max_block_size_for(psc_context *ctx, long n, double io_bytes) {
   // single block: 40 B/symbol of sort state (keys, values, SA)
   if ((double)n * 40.0 <= avail && n <= (1L << 31) - 4096) return n;
   // several blocks: every block's SA and gap array stay until the final merge (8n), gt bits (n/4), the merge
-  // scratch of one output chunk (planes + scanned gaps: 18 B per slot), the rank stream of one walk chunk
-  // (2 x 4 B x 2^29 positions at most, walk.cu); per block symbol 40 B of sort state, or BWT + rank planes
+  // scratch of one output chunk (at most 18 B per slot), the rank pages of one walk chunk (8 B x 2^29
+  // positions at most, walk.cu); per block symbol 40 B of sort state, or BWT + rank planes
   // (<= 255 * 32/224 B) while streaming
   const double chunk = (double)std::min(n, merge_chunk_entries());
   double rest = avail - 8.3 * (double)n - 18.0 * chunk - 8.0 * (double)std::min(n, 1L << 29);
